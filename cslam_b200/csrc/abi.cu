@@ -1,0 +1,622 @@
+// C-ABI of the matcher (include/cslam_nns.h).  Host-side logic only: storage, staging, variant
+// dispatch.  The arithmetic is in k1_single.cu / k2_batched.cu / k3_sort.cu / k4_merge.cu.
+#include <stdlib.h>
+#include <string.h>
+
+#include <atomic>
+#include <cmath>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../include/cslam_nns.h"
+#include "arena.h"
+#include "kernels.h"
+
+namespace cslam {
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+}  // namespace cslam
+
+using namespace cslam;
+
+namespace {
+
+std::string g_create_error;
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  bool ensure(size_t want) {
+    if (want <= bytes) return true;
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+    size_t sz = want < 4096 ? 4096 : want;
+    if (cudaMalloc(&p, sz) != cudaSuccess) {
+      cudaGetLastError();
+      return false;
+    }
+    bytes = sz;
+    return true;
+  }
+  void free() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+};
+
+struct PinBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  bool ensure(size_t want) {
+    if (want <= bytes) return true;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    bytes = 0;
+    size_t sz = want < 4096 ? 4096 : want;
+    if (cudaHostAlloc(&p, sz, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+      cudaGetLastError();
+      return false;
+    }
+    bytes = sz;
+    return true;
+  }
+  void free() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    bytes = 0;
+  }
+};
+
+}  // namespace
+
+struct cslam_nns_s {
+  int device = 0;
+  int num_sms = 148;
+  long long dim = 0, ld = 0;
+  long long n = 0;
+  long long capacity = 0;   // logical rows, reference sequence initial * 2^j
+  long long initial = 1000;
+  Arena arena;
+  std::string err;
+  int variant = 0, last_variant = 0;
+  K1Tuning k1;
+  // device scratch
+  DevBuf q, q_lo, inv_qn, scratch, ticket, part_keys, res_dev, all_sims, sort_tmp, sort_kv;
+  PinBuf res_host;
+  // optional per-kernel timing (cslam_nns_profile)
+  bool profile = false;
+  std::vector<cudaEvent_t> ev;   // pairs
+  size_t ev_used = 0;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+int fail(cslam_nns_t h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  else g_create_error = msg;
+  return code;
+}
+int fail_cuda(cslam_nns_t h, const char* what, cudaError_t e) {
+  cudaGetLastError();
+  return fail(h, CSLAM_NNS_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(h, call)                                   \
+  do {                                                \
+    cudaError_t e__ = (call);                         \
+    if (e__ != cudaSuccess) return fail_cuda(h, #call, e__); \
+  } while (0)
+
+int grow_to(cslam_nns_t h, long long rows, cudaStream_t stream) {
+  if (h->dim <= 0) return fail(h, CSLAM_NNS_ESTATE, "descriptor size not set");
+  long long cap = h->capacity > 0 ? h->capacity : h->initial;
+  while (cap < rows) cap *= 2;  // nns_matching.py:38 doubles
+  if (cap == h->capacity) return 0;
+  const size_t bytes = (size_t)cap * h->ld * 4;
+  std::string err;
+  if (!h->arena.ensure(h->device, bytes, stream, &err)) return fail(h, CSLAM_NNS_ENOMEM, err);
+  h->capacity = cap;
+  return 0;
+}
+
+struct KernelTimer {
+  cslam_nns_t h;
+  cudaStream_t stream;
+  cudaEvent_t stop = nullptr;
+  KernelTimer(cslam_nns_t h_, cudaStream_t s) : h(h_), stream(s) {
+    if (!h->profile) return;
+    if (h->ev_used + 2 > h->ev.size()) {
+      cudaEvent_t a, b;
+      if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+      h->ev.push_back(a);
+      h->ev.push_back(b);
+    }
+    cudaEventRecord(h->ev[h->ev_used], stream);
+    stop = h->ev[h->ev_used + 1];
+    h->ev_used += 2;
+  }
+  ~KernelTimer() {
+    if (stop) cudaEventRecord(stop, stream);
+  }
+};
+
+__global__ void fill_kernel(long long* idx, float* sim, long long B, int k, int from) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int w = k - from;
+  if (i >= B * w) return;
+  const long long b = i / w;
+  const int j = from + (int)(i - b * w);
+  if (idx) idx[b * k + j] = -1;
+  if (sim) sim[b * k + j] = -INFINITY;
+}
+
+// Run the search for B device-resident queries (pitch q_ld) and write k_run entries per query to
+// device-accessible out pointers (pitch k_run).  Any of the three outputs may be null.
+int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, int k_run,
+                  u64* o_keys, long long* o_idx, float* o_sim, long long idx_stride,
+                  long long idx_offset, cudaStream_t stream) {
+  int variant = h->variant;
+  if (variant == 0) {
+    if (k_run > kK1MaxK) variant = 3;
+    else if (B >= 2 && k2_supported((int)(B > kK2MaxBatch ? kK2MaxBatch : B), k_run)) variant = 2;
+    else variant = 1;
+  }
+  if (variant == 2 && !k2_supported((int)(B > kK2MaxBatch ? kK2MaxBatch : B), k_run))
+    return fail(h, CSLAM_NNS_EINVAL, "k does not fit the batched kernel's fused select");
+  if (variant == 1 && k_run > kK1MaxK)
+    return fail(h, CSLAM_NNS_EINVAL, "k exceeds the fused single-query select (128)");
+  h->last_variant = variant;
+
+  if (!h->ticket.p) {
+    if (!h->ticket.ensure(64)) return fail(h, CSLAM_NNS_ENOMEM, "scratch allocation failed");
+    CK(h, cudaMemsetAsync(h->ticket.p, 0, 64, stream));  // the kernels leave it at zero again
+  }
+  if (!h->scratch.ensure((size_t)k1_max_grid(h->num_sms) * kK1MaxK * 8))
+    return fail(h, CSLAM_NNS_ENOMEM, "scratch allocation failed");
+
+  if (variant == 1) {
+    for (long long b = 0; b < B; ++b) {
+      K1Args a;
+      a.db = (const float*)h->arena.base();
+      a.n = h->n;
+      a.ld = (int)h->ld;
+      a.dim = (int)h->dim;
+      a.q = dq + b * q_ld;
+      a.k = k_run;
+      a.scratch = (u64*)h->scratch.p;
+      a.ticket = (unsigned*)h->ticket.p;
+      a.out_keys = o_keys ? o_keys + b * k_run : nullptr;
+      a.out_idx = o_idx ? o_idx + b * k_run : nullptr;
+      a.out_sim = o_sim ? o_sim + b * k_run : nullptr;
+      a.idx_stride = idx_stride;
+      a.idx_offset = idx_offset;
+      a.all_sims = nullptr;
+      KernelTimer kt(h, stream);
+      CK(h, k1_launch(a, h->k1, h->num_sms, stream));
+    }
+    return 0;
+  }
+  if (variant == 3) {
+    const long long n = h->n;
+    if (!h->all_sims.ensure((size_t)n * 4) || !h->sort_kv.ensure((size_t)n * 16))
+      return fail(h, CSLAM_NNS_ENOMEM, "two-pass buffers");
+    const size_t tb = sort_temp_bytes(n);
+    if (!h->sort_tmp.ensure(tb)) return fail(h, CSLAM_NNS_ENOMEM, "sort temp");
+    uint32_t* kv = (uint32_t*)h->sort_kv.p;
+    for (long long b = 0; b < B; ++b) {
+      K1Args a;
+      a.db = (const float*)h->arena.base();
+      a.n = n;
+      a.ld = (int)h->ld;
+      a.dim = (int)h->dim;
+      a.q = dq + b * q_ld;
+      a.k = 1;
+      a.scratch = (u64*)h->scratch.p;
+      a.ticket = (unsigned*)h->ticket.p;
+      a.out_keys = nullptr;
+      a.out_idx = nullptr;
+      a.out_sim = nullptr;
+      a.idx_stride = 1;
+      a.idx_offset = 0;
+      a.all_sims = (float*)h->all_sims.p;
+      CK(h, k1_launch(a, h->k1, h->num_sms, stream));
+      CK(h, sort_select((const float*)h->all_sims.p, n, k_run, h->sort_tmp.p, tb, kv, kv + n,
+                        kv + 2 * n, kv + 3 * n, o_keys ? o_keys + b * k_run : nullptr,
+                        o_idx ? o_idx + b * k_run : nullptr, o_sim ? o_sim + b * k_run : nullptr,
+                        idx_stride, idx_offset, stream));
+    }
+    return 0;
+  }
+  // variant 2: tcgen05 batched kernel, <= 256 queries per pass
+  const DriverApi& d = driver_api();
+  if (!d.tensorMapEncodeTiled) return fail(h, CSLAM_NNS_ECUDA, "cuTensorMapEncodeTiled unavailable");
+  const int grid = k2_grid(h->n, h->num_sms);
+  for (long long b0 = 0; b0 < B; b0 += kK2MaxBatch) {
+    const int Bc = (int)((B - b0) > kK2MaxBatch ? kK2MaxBatch : (B - b0));
+    if (!h->q_lo.ensure((size_t)Bc * q_ld * 4) || !h->inv_qn.ensure((size_t)Bc * 4) ||
+        !h->part_keys.ensure((size_t)grid * Bc * k_run * 8))
+      return fail(h, CSLAM_NNS_ENOMEM, "batched scratch");
+    const float* qc = dq + b0 * q_ld;
+    CK(h, k2_prepare(qc, Bc, (int)h->dim, (int)q_ld, (float*)h->q_lo.p, (float*)h->inv_qn.p, stream));
+    K2Args a;
+    a.db = (const float*)h->arena.base();
+    a.n = h->n;
+    a.ld = (int)h->ld;
+    a.dim = (int)h->dim;
+    a.q_hi = qc;
+    a.q_lo = (const float*)h->q_lo.p;
+    a.inv_qn = (const float*)h->inv_qn.p;
+    a.q_ld = (int)q_ld;
+    a.B = Bc;
+    a.k = k_run;
+    a.part_keys = (u64*)h->part_keys.p;
+    a.encode_fn = d.tensorMapEncodeTiled;
+    const char* kerr = nullptr;
+    cudaError_t e;
+    {
+      KernelTimer kt(h, stream);
+      e = k2_launch(a, h->num_sms, stream, &kerr);
+    }
+    if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch", e);
+    CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run,
+                   o_keys ? o_keys + b0 * k_run : nullptr, o_idx ? o_idx + b0 * k_run : nullptr,
+                   o_sim ? o_sim + b0 * k_run : nullptr, idx_stride, idx_offset, stream));
+  }
+  return 0;
+}
+
+// Bring the queries to device memory with a 16-byte aligned pitch (multiple of 4 floats).
+int stage_queries(cslam_nns_t h, const float* queries, long long B, long long q_ld, int src_is_device,
+                  cudaStream_t stream, const float** dq, long long* dq_ld) {
+  const long long dim = h->dim;
+  if (q_ld <= 0) q_ld = dim;
+  if (q_ld < dim) return fail(h, CSLAM_NNS_EINVAL, "query pitch smaller than dim");
+  if (src_is_device && (q_ld % 4 == 0) && ((uintptr_t)queries % 16 == 0)) {
+    *dq = queries;
+    *dq_ld = q_ld;
+    return 0;
+  }
+  const long long pld = h->ld;
+  if (!h->q.ensure((size_t)B * pld * 4)) return fail(h, CSLAM_NNS_ENOMEM, "query staging");
+  if (pld != dim) CK(h, cudaMemsetAsync(h->q.p, 0, (size_t)B * pld * 4, stream));
+  CK(h, cudaMemcpy2DAsync(h->q.p, (size_t)pld * 4, queries, (size_t)q_ld * 4, (size_t)dim * 4,
+                          (size_t)B, src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                          stream));
+  *dq = (const float*)h->q.p;
+  *dq_ld = pld;
+  return 0;
+}
+
+}  // namespace
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+int cslam_nns_abi_version(void) { return 1; }
+int64_t cslam_nns_launch_count(void) { return g_launches.load(); }
+
+const char* cslam_nns_last_error(cslam_nns_t h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nns_t* out) {
+  if (!out) return fail(nullptr, CSLAM_NNS_EINVAL, "out is NULL");
+  *out = nullptr;
+  if (dim < 0) return fail(nullptr, CSLAM_NNS_EINVAL, "dim must be >= 0");
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return fail(nullptr, CSLAM_NNS_ENODEV,
+                std::string("no CUDA device available (") +
+                    (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                    "); this library has no CPU fallback");
+  }
+  if (device < 0 || device >= count) return fail(nullptr, CSLAM_NNS_EINVAL, "bad device ordinal");
+  int major = 0, sms = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  if (major != 10)
+    return fail(nullptr, CSLAM_NNS_ENODEV,
+                "device is not compute capability 10.x; kernels are built for sm_100a only");
+  DeviceGuard g(device);
+  cudaFree(0);
+  cslam_nns_t h = new cslam_nns_s();
+  h->device = device;
+  h->num_sms = sms;
+  h->initial = initial_capacity > 0 ? initial_capacity : 1000;
+  h->k1.stage_bytes = env_int("CSLAM_K1_STAGE_BYTES", 8192);
+  h->k1.stages = env_int("CSLAM_K1_STAGES", 3);
+  h->k1.ctas = env_int("CSLAM_K1_CTAS", 0);
+  h->variant = env_int("CSLAM_NNS_VARIANT", 0);
+  *out = h;
+  if (dim > 0) {
+    int rc = cslam_nns_set_dim(h, dim);
+    if (rc == 0) rc = grow_to(h, h->initial, 0);
+    if (rc != 0) {
+      g_create_error = h->err;
+      delete h;
+      *out = nullptr;
+      return rc;
+    }
+  }
+  return 0;
+}
+
+int cslam_nns_destroy(cslam_nns_t h) {
+  if (!h) return 0;
+  {
+    DeviceGuard g(h->device);
+    cudaDeviceSynchronize();
+    h->arena.release();
+    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket,
+                      &h->part_keys, &h->res_dev, &h->all_sims, &h->sort_tmp, &h->sort_kv};
+    for (DevBuf* b : bufs) b->free();
+    h->res_host.free();
+    for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
+  }
+  delete h;
+  return 0;
+}
+
+int cslam_nns_set_dim(cslam_nns_t h, int64_t dim) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (dim <= 0) return fail(h, CSLAM_NNS_EINVAL, "dim must be positive");
+  if (h->dim > 0) return h->dim == dim ? 0 : fail(h, CSLAM_NNS_ESTATE, "dim already set");
+  h->dim = dim;
+  h->ld = (dim + 3) / 4 * 4;
+  return 0;
+}
+
+int cslam_nns_reserve(cslam_nns_t h, int64_t rows) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  DeviceGuard g(h->device);
+  return grow_to(h, rows, 0);
+}
+
+int64_t cslam_nns_size(cslam_nns_t h) { return h ? h->n : -1; }
+int64_t cslam_nns_capacity(cslam_nns_t h) { return h ? h->capacity : -1; }
+int64_t cslam_nns_dim(cslam_nns_t h) { return h ? h->dim : -1; }
+int64_t cslam_nns_ld(cslam_nns_t h) { return h ? h->ld : -1; }
+void* cslam_nns_data_ptr(cslam_nns_t h) { return h ? h->arena.base() : nullptr; }
+int cslam_nns_device(cslam_nns_t h) { return h ? h->device : -1; }
+
+int cslam_nns_add(cslam_nns_t h, const float* rows, int64_t count, int64_t src_ld, int src_is_device,
+                  void* stream_, int64_t* new_n) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (count < 0 || (count > 0 && !rows)) return fail(h, CSLAM_NNS_EINVAL, "bad rows/count");
+  if (h->dim <= 0) return fail(h, CSLAM_NNS_ESTATE, "descriptor size not set");
+  if (src_ld <= 0) src_ld = h->dim;
+  if (src_ld < h->dim) return fail(h, CSLAM_NNS_EINVAL, "source pitch smaller than dim");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h->device);
+  if (count > 0) {
+    if (h->n + count > 0xffffffffll) return fail(h, CSLAM_NNS_EINVAL, "more than 2^32 rows");
+    int rc = grow_to(h, h->n + count, stream);
+    if (rc) return rc;
+    float* dst = (float*)h->arena.base() + (size_t)h->n * h->ld;
+    // plain DMA: the pad lanes [dim, ld) were zeroed when the chunk was mapped and are never written
+    CK(h, cudaMemcpy2DAsync(dst, (size_t)h->ld * 4, rows, (size_t)src_ld * 4, (size_t)h->dim * 4,
+                            (size_t)count,
+                            src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream));
+    h->n += count;
+  }
+  if (new_n) *new_n = h->n;
+  return 0;
+}
+
+int cslam_nns_search(cslam_nns_t h, const float* queries, int64_t B, int64_t q_ld, int src_is_device,
+                     int k, int64_t* out_idx, float* out_sim, int dst_is_device, void* stream_,
+                     int64_t* out_kk) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (B < 0 || k < 0 || (B > 0 && !queries)) return fail(h, CSLAM_NNS_EINVAL, "bad queries/B/k");
+  if (h->dim <= 0) return fail(h, CSLAM_NNS_ESTATE, "descriptor size not set");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h->device);
+  const long long kk = k < h->n ? k : h->n;
+  if (out_kk) *out_kk = kk;
+  if (B == 0 || k == 0) return 0;
+
+  if (kk == 0) {  // empty DB: nothing but fill
+    if (dst_is_device) {
+      const long long tot = B * k;
+      fill_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>((long long*)out_idx, out_sim, B, k, 0);
+      count_launch();
+      CK(h, cudaGetLastError());
+    } else {
+      for (long long i = 0; i < B * k; ++i) {
+        if (out_idx) out_idx[i] = -1;
+        if (out_sim) out_sim[i] = -std::numeric_limits<float>::infinity();
+      }
+    }
+    return 0;
+  }
+  const int k_run = (int)kk;
+  const float* dq;
+  long long dq_ld;
+  int rc = stage_queries(h, queries, B, q_ld, src_is_device, stream, &dq, &dq_ld);
+  if (rc) return rc;
+
+  if (dst_is_device) {
+    if (k_run == k) return search_device(h, dq, B, dq_ld, k_run, nullptr, (long long*)out_idx, out_sim, 1, 0, stream);
+    if (!h->res_dev.ensure((size_t)B * k_run * 12)) return fail(h, CSLAM_NNS_ENOMEM, "result buffer");
+    long long* di = (long long*)h->res_dev.p;
+    float* ds = (float*)(di + B * k_run);
+    rc = search_device(h, dq, B, dq_ld, k_run, nullptr, di, ds, 1, 0, stream);
+    if (rc) return rc;
+    if (out_idx)
+      CK(h, cudaMemcpy2DAsync(out_idx, (size_t)k * 8, di, (size_t)k_run * 8, (size_t)k_run * 8, B,
+                              cudaMemcpyDeviceToDevice, stream));
+    if (out_sim)
+      CK(h, cudaMemcpy2DAsync(out_sim, (size_t)k * 4, ds, (size_t)k_run * 4, (size_t)k_run * 4, B,
+                              cudaMemcpyDeviceToDevice, stream));
+    const long long tot = B * (k - k_run);
+    fill_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>((long long*)out_idx, out_sim, B, k, k_run);
+    count_launch();
+    CK(h, cudaGetLastError());
+    return 0;
+  }
+
+  // host destination: kernels write into mapped pinned memory, one stream sync, then a host copy
+  if (!h->res_host.ensure((size_t)B * k_run * 12)) return fail(h, CSLAM_NNS_ENOMEM, "pinned result buffer");
+  long long* hi = (long long*)h->res_host.p;
+  float* hs = (float*)(hi + B * k_run);
+  rc = search_device(h, dq, B, dq_ld, k_run, nullptr, hi, hs, 1, 0, stream);
+  if (rc) return rc;
+  CK(h, cudaStreamSynchronize(stream));
+  for (long long b = 0; b < B; ++b) {
+    if (out_idx) {
+      memcpy(out_idx + b * k, hi + b * k_run, (size_t)k_run * 8);
+      for (int j = k_run; j < k; ++j) out_idx[b * k + j] = -1;
+    }
+    if (out_sim) {
+      memcpy(out_sim + b * k, hs + b * k_run, (size_t)k_run * 4);
+      for (int j = k_run; j < k; ++j) out_sim[b * k + j] = -std::numeric_limits<float>::infinity();
+    }
+  }
+  return 0;
+}
+
+int cslam_nns_search_keys(cslam_nns_t h, const float* queries, int64_t B, int64_t q_ld,
+                          int src_is_device, int k, int64_t row_stride, int64_t row_offset,
+                          uint64_t* out_keys_dev, void* stream_) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (B <= 0 || k <= 0 || !queries || !out_keys_dev) return fail(h, CSLAM_NNS_EINVAL, "bad arguments");
+  if (k > kK1MaxK) return fail(h, CSLAM_NNS_EINVAL, "sharded search supports k <= 128");
+  if (h->dim <= 0) return fail(h, CSLAM_NNS_ESTATE, "descriptor size not set");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h->device);
+  if (h->n == 0) {
+    CK(h, cudaMemsetAsync(out_keys_dev, 0, (size_t)B * k * 8, stream));
+    return 0;
+  }
+  const float* dq;
+  long long dq_ld;
+  int rc = stage_queries(h, queries, B, q_ld, src_is_device, stream, &dq, &dq_ld);
+  if (rc) return rc;
+  return search_device(h, dq, B, dq_ld, k, (u64*)out_keys_dev, nullptr, nullptr, row_stride,
+                       row_offset, stream);
+}
+
+int cslam_nns_merge_keys(int device, const uint64_t* keys_dev, int parts, int64_t B, int k,
+                         int64_t* out_idx, float* out_sim, int dst_is_device, void* stream_,
+                         int64_t* out_kk) {
+  if (!keys_dev || parts <= 0 || B <= 0 || k <= 0 || k > kK1MaxK) {
+    g_create_error = "bad arguments to cslam_nns_merge_keys";
+    return CSLAM_NNS_EINVAL;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(device);
+  if (dst_is_device) {
+    cudaError_t e = k4_merge((const u64*)keys_dev, parts, B, k, k, nullptr, (long long*)out_idx,
+                             out_sim, 1, 0, stream);
+    if (e != cudaSuccess) return fail_cuda(nullptr, "k4_merge", e);
+    return 0;
+  }
+  void* pin = nullptr;
+  if (cudaHostAlloc(&pin, (size_t)B * k * 12, cudaHostAllocMapped) != cudaSuccess)
+    return fail(nullptr, CSLAM_NNS_ENOMEM, "pinned result buffer");
+  long long* hi = (long long*)pin;
+  float* hs = (float*)(hi + B * k);
+  cudaError_t e = k4_merge((const u64*)keys_dev, parts, B, k, k, nullptr, hi, hs, 1, 0, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  if (e != cudaSuccess) {
+    cudaFreeHost(pin);
+    return fail_cuda(nullptr, "k4_merge", e);
+  }
+  if (out_idx) memcpy(out_idx, hi, (size_t)B * k * 8);
+  if (out_sim) memcpy(out_sim, hs, (size_t)B * k * 4);
+  if (out_kk) {
+    long long c = 0;
+    while (c < k && hi[c] >= 0) ++c;
+    *out_kk = c;
+  }
+  cudaFreeHost(pin);
+  return 0;
+}
+
+int cslam_nns_profile(cslam_nns_t h, int enable) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  h->profile = enable != 0;
+  return 0;
+}
+
+int cslam_nns_profile_read(cslam_nns_t h, float* ms_total, int64_t* launches) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  DeviceGuard g(h->device);
+  float total = 0.f;
+  for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
+    CK(h, cudaEventSynchronize(h->ev[i + 1]));
+    float ms = 0.f;
+    CK(h, cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+    total += ms;
+  }
+  if (ms_total) *ms_total = total;
+  if (launches) *launches = (int64_t)(h->ev_used / 2);
+  h->ev_used = 0;
+  return 0;
+}
+
+int cslam_nns_set_variant(cslam_nns_t h, int variant) {
+  if (!h || variant < 0 || variant > 3) return CSLAM_NNS_EINVAL;
+  h->variant = variant;
+  return 0;
+}
+int cslam_nns_last_variant(cslam_nns_t h) { return h ? h->last_variant : -1; }
+
+int cslam_nns_time_search(cslam_nns_t h, const float* queries_dev, int64_t B, int64_t q_ld, int k,
+                          int iters, void* stream_, float* ms_per_search) {
+  if (!h || !queries_dev || B <= 0 || k <= 0 || iters <= 0 || !ms_per_search)
+    return fail(h, CSLAM_NNS_EINVAL, "bad arguments");
+  if (h->n == 0) return fail(h, CSLAM_NNS_ESTATE, "empty database");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h->device);
+  const int k_run = (int)(k < h->n ? k : h->n);
+  const float* dq;
+  long long dq_ld;
+  int rc = stage_queries(h, queries_dev, B, q_ld, 1, stream, &dq, &dq_ld);
+  if (rc) return rc;
+  if (!h->res_dev.ensure((size_t)B * k_run * 12)) return fail(h, CSLAM_NNS_ENOMEM, "result buffer");
+  long long* di = (long long*)h->res_dev.p;
+  float* ds = (float*)(di + B * k_run);
+  cudaEvent_t e0, e1;
+  CK(h, cudaEventCreate(&e0));
+  CK(h, cudaEventCreate(&e1));
+  rc = search_device(h, dq, B, dq_ld, k_run, nullptr, di, ds, 1, 0, stream);  // warm
+  if (rc == 0) {
+    cudaEventRecord(e0, stream);
+    for (int i = 0; i < iters && rc == 0; ++i)
+      rc = search_device(h, dq, B, dq_ld, k_run, nullptr, di, ds, 1, 0, stream);
+    cudaEventRecord(e1, stream);
+    cudaError_t e = cudaEventSynchronize(e1);
+    if (rc == 0 && e != cudaSuccess) rc = fail_cuda(h, "cudaEventSynchronize", e);
+    float ms = 0.f;
+    if (rc == 0) {
+      cudaEventElapsedTime(&ms, e0, e1);
+      *ms_per_search = ms / iters;
+    }
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return rc;
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

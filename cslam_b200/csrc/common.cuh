@@ -1,0 +1,237 @@
+// Shared device helpers for the cslam NNS kernels (sm_100a only).
+//
+// Key encoding.  Every candidate is one 64-bit key
+//     key = orderable(sim) << 32 | ~row            (row < 2^32)
+// so that "larger key" == "higher similarity, then lower row index".  orderable() is the usual
+// monotone float->uint map; NaN is canonicalised to 0xFFFFFFFF so it sorts FIRST, which is what
+// torch.argsort(descending=True) does at cslam/nns_matching.py:62.  key 0 can never be produced by
+// a real candidate and marks an empty slot.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cslam {
+
+typedef unsigned long long u64;
+
+static constexpr float kEps = 1e-8f;  // torch cosine_similarity eps (nns_matching.py:61)
+static constexpr unsigned kFull = 0xffffffffu;
+
+__host__ __device__ __forceinline__ uint32_t sim_to_ord(float s) {
+#ifdef __CUDA_ARCH__
+  uint32_t b = __float_as_uint(s);
+#else
+  uint32_t b;
+  memcpy(&b, &s, 4);
+#endif
+  if ((b & 0x7fffffffu) > 0x7f800000u) return 0xffffffffu;  // NaN sorts first
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+__host__ __device__ __forceinline__ float ord_to_sim(uint32_t o) {
+  uint32_t b;
+  if (o == 0xffffffffu) b = 0x7fc00000u;
+  else b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+#endif
+}
+
+__host__ __device__ __forceinline__ u64 make_key(float sim, uint32_t row) {
+  return ((u64)sim_to_ord(sim) << 32) | (u64)(~row);
+}
+__host__ __device__ __forceinline__ uint32_t key_row(u64 key) { return ~(uint32_t)key; }
+__host__ __device__ __forceinline__ float key_sim(u64 key) { return ord_to_sim((uint32_t)(key >> 32)); }
+
+// ------------------------------------------------------------------------------------------------
+// Warp-level top-k list kept in shared memory: `list[0..k)` sorted descending, empty slots = 0.
+// All 32 lanes call these together with identical (warp-uniform) arguments.
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ void warp_list_clear(u64* list, int k, int lane) {
+  for (int i = lane; i < k; i += 32) list[i] = 0ull;
+  __syncwarp();
+}
+
+// Insert `key` (warp-uniform) if it beats the current k-th entry.  `thr` mirrors list[k-1].
+__device__ __forceinline__ void warp_list_insert(u64* list, int k, u64 key, u64& thr, int lane) {
+  if (key <= thr) return;
+  int pos = 0;
+  for (int base = 0; base < k; base += 32) {
+    int i = base + lane;
+    bool gt = (i < k) && (list[i] > key);
+    pos += __popc(__ballot_sync(kFull, gt));
+  }
+  // shift [pos, k-2] -> [pos+1, k-1], highest chunk first so every read sees pre-shift data
+  for (int base = ((k - 1) >> 5) << 5; base >= 0; base -= 32) {
+    int i = base + lane;
+    bool act = (i < k) && (i > pos);
+    u64 v = 0ull;
+    if (act) v = list[i - 1];
+    __syncwarp();
+    if (act) list[i] = v;
+    __syncwarp();
+  }
+  if (lane == 0) list[pos] = key;
+  __syncwarp();
+  thr = list[k - 1];
+}
+
+// Offer one key per lane (`have` says whether this lane's key is real).
+__device__ __forceinline__ void warp_list_offer(u64* list, int k, u64 key, bool have, u64& thr,
+                                                int lane) {
+  unsigned m = __ballot_sync(kFull, have && key > thr);
+  while (m) {
+    int src = __ffs(m) - 1;
+    m &= m - 1;
+    u64 cand = __shfl_sync(kFull, key, src);
+    warp_list_insert(list, k, cand, thr, lane);
+  }
+}
+
+// Stream `count` keys from memory (global or shared) into the list.
+__device__ __forceinline__ void warp_list_stream(u64* list, int k, u64& thr, const u64* src,
+                                                 int64_t count, int lane) {
+  for (int64_t base = 0; base < count; base += 32) {
+    int64_t i = base + lane;
+    u64 key = 0ull;
+    bool have = i < count;
+    if (have) key = src[i];
+    warp_list_offer(list, k, key, have && key != 0ull, thr, lane);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// PTX wrappers: mbarrier, bulk async copy (TMA 1-D), TMA 2-D tiles, tcgen05.
+// ------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// generic-proxy accesses before this point are ordered before later async-proxy accesses
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// 1-D bulk copy global -> shared, completion signalled on `bar` (SASS: UBLKCP).
+// dst, src and bytes must be multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// 2-D tiled TMA load (SASS: UTMALDG).  c0 = innermost (column) coordinate, c1 = row coordinate.
+__device__ __forceinline__ void tma_load_2d(void* dst, const void* tmap, int c0, int c1,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, "
+      "{%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+// -- tcgen05 ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(dst_smem)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols)
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], tf32 inputs, fp32 accumulate.  One thread issues.
+__device__ __forceinline__ void umma_tf32_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                             uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrive once all previously issued tcgen05.mma of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+// 32 lanes x 8 consecutive columns: thread t of the warp gets lane (base_lane + t)
+__device__ __forceinline__ void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+}  // namespace cslam

@@ -1,0 +1,60 @@
+// K4 — merge `parts` sorted key lists per query into one top-k list and decode it.
+// Used (a) after the batched kernel K2 (parts = its grid), (b) after the all-gather of the
+// row-sharded search (parts = world size) and (c) by the looped single-query path.
+// The merge is a thresholded stream into a warp-held sorted list (common.cuh), so the result is the
+// k largest 64-bit keys regardless of how the candidates were partitioned: identical output for any
+// shard count or grid size.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace cslam {
+namespace {
+
+constexpr int W4 = 4;
+
+__global__ void __launch_bounds__(W4 * 32) k4_kernel(const u64* __restrict__ keys, int parts,
+                                                     long long B, int k_in, int k_out,
+                                                     u64* out_keys, long long* out_idx,
+                                                     float* out_sim, long long idx_stride,
+                                                     long long idx_offset) {
+  extern __shared__ __align__(16) unsigned char smem4[];
+  u64* lists = reinterpret_cast<u64*>(smem4);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long b = blockIdx.x;
+  u64* my_list = lists + (size_t)warp * k_out;
+  warp_list_clear(my_list, k_out, lane);
+  u64 thr = 0ull;
+  for (int p = warp; p < parts; p += W4) {
+    const u64* src = keys + ((size_t)p * B + b) * k_in;
+    warp_list_stream(my_list, k_out, thr, src, k_in, lane);
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  for (int w = 1; w < W4; ++w)
+    warp_list_stream(my_list, k_out, thr, lists + (size_t)w * k_out, k_out, lane);
+  for (int i = lane; i < k_out; i += 32) {
+    const u64 key = my_list[i];
+    const bool have = key != 0ull;
+    const long long grow = (long long)key_row(key) * idx_stride + idx_offset;
+    const size_t o = (size_t)b * k_out + i;
+    if (out_keys)
+      out_keys[o] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
+    if (out_idx) out_idx[o] = have ? grow : -1ll;
+    if (out_sim) out_sim[o] = have ? key_sim(key) : -INFINITY;
+  }
+}
+
+}  // namespace
+
+cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_out, u64* out_keys,
+                     long long* out_idx, float* out_sim, long long idx_stride,
+                     long long idx_offset, cudaStream_t stream) {
+  if (B <= 0 || k_out <= 0) return cudaSuccess;
+  const size_t smem = (size_t)W4 * k_out * 8;
+  k4_kernel<<<(unsigned)B, W4 * 32, smem, stream>>>(keys, parts, B, k_in, k_out, out_keys, out_idx,
+                                                    out_sim, idx_stride, idx_offset);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace cslam

@@ -1,0 +1,81 @@
+// Internal launch interface between the C-ABI (abi.cu) and the kernels.  Not installed.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cslam {
+
+typedef unsigned long long u64;
+
+// ---- K1: fused single-query cosine GEMV + warp top-k (k1_single.cu) ---------------------------
+static constexpr int kK1Warps = 8;
+static constexpr int kK1MaxK = 128;  // largest k the fused select handles
+
+struct K1Tuning {
+  int stage_bytes;  // bytes per bulk copy (per warp, per stage)
+  int stages;       // ring depth per warp
+  int ctas;         // grid size cap (0 = number of SMs)
+};
+
+struct K1Args {
+  const float* db;
+  long long n;
+  int ld;  // row pitch in floats, multiple of 4
+  int dim;
+  const float* q;  // device, dim floats
+  int k;
+  u64* scratch;      // [grid][k]
+  unsigned* ticket;  // zero before launch; reset by the kernel
+  u64* out_keys;     // [k] or null
+  long long* out_idx;
+  float* out_sim;
+  long long idx_stride, idx_offset;
+  float* all_sims;  // non-null: write every row's similarity, skip the select
+};
+
+// Maximum grid K1 will ever use on `device` (sizes the scratch buffer).
+int k1_max_grid(int num_sms);
+cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStream_t stream);
+
+// ---- two-pass select for k > kK1MaxK (k3_sort.cu) ----------------------------------------------
+// all_sims[n] -> out (k best), using a device radix sort.  temp storage is owned by the caller.
+size_t sort_temp_bytes(long long n);
+cudaError_t sort_select(const float* all_sims, long long n, int k, void* temp, size_t temp_bytes,
+                        uint32_t* keys_a, uint32_t* keys_b, uint32_t* idx_a, uint32_t* idx_b,
+                        u64* out_keys, long long* out_idx, float* out_sim, long long idx_stride,
+                        long long idx_offset, cudaStream_t stream);
+
+// ---- K4: merge `parts` key lists per query and decode (k4_merge.cu) -----------------------------
+// keys laid out [parts][B][k_in]; writes B x k_out (k_out <= k_in is fine).
+cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_out, u64* out_keys,
+                     long long* out_idx, float* out_sim, long long idx_stride,
+                     long long idx_offset, cudaStream_t stream);
+
+// ---- K2: batched tcgen05 3xTF32 GEMM + fused per-query top-k (k2_batched.cu) --------------------
+static constexpr int kK2MaxBatch = 256;  // queries per pass (UMMA N)
+static constexpr int kK2ListBudget = 2560;  // k * padded batch must not exceed this (smem lists)
+
+struct K2Args {
+  const float* db;
+  long long n;
+  int ld, dim;
+  const float* q_hi;   // device [B][q_ld] raw fp32 queries
+  const float* q_lo;   // device [B][q_ld] tf32 residuals (written by k2_prepare)
+  const float* inv_qn; // device [B]
+  int q_ld;
+  int B;               // <= kK2MaxBatch
+  int k;
+  u64* part_keys;      // [grid][B][k] scratch
+  void* encode_fn;     // cuTensorMapEncodeTiled entry point
+};
+bool k2_supported(int B, int k);
+int k2_grid(long long n, int num_sms);
+// queries (device, pitch q_ld) -> q_lo, inv_qn
+cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_lo, float* inv_qn,
+                       cudaStream_t stream);
+cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err);
+
+// launch counter shared by all kernels (reported through cslam_nns_launch_count)
+void count_launch(int n = 1);
+
+}  // namespace cslam

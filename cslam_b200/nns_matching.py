@@ -1,0 +1,212 @@
+"""Drop-in replacement for ``cslam.nns_matching.NearestNeighborsMatching``.
+
+Same constructor, methods, return types and public attributes as the reference class
+(``/root/reference/cslam/nns_matching.py:5-78``); underneath, the descriptor database lives in a
+growable HBM arena owned by ``libcslam_nns.so`` and every search is one hand-written sm_100a kernel
+(see ``include/cslam_nns.h`` and ``DESIGN.md``).  PyTorch is used only for the current CUDA stream,
+for exposing ``.data`` as a tensor view and for converting inputs exactly like the reference does.
+
+Additive API (does not change any reference signature): ``add_items``, ``search_batch`` and
+``search`` accepting a ``(B, dim)`` query.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _native
+
+
+class _CudaArrayView:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can alias the arena without a copy."""
+
+    def __init__(self, ptr, shape, strides, owner):
+        self.__cuda_array_interface__ = {
+            "shape": tuple(shape),
+            "typestr": "<f4",
+            "data": (int(ptr), False),
+            "strides": tuple(strides),
+            "version": 3,
+        }
+        self._owner = owner  # keeps the native handle alive as long as the view is
+
+
+class _Handle:
+    """Owns the native handle; destroyed when the last Python reference goes away."""
+
+    def __init__(self, device_index, dim):
+        self.lib = _native.load()
+        self.h = ctypes.c_void_p()
+        rc = self.lib.cslam_nns_create(int(device_index), int(dim or 0), 0, ctypes.byref(self.h))
+        _native.check(rc, None)
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None) is not None and self.h.value:
+                self.lib.cslam_nns_destroy(self.h)
+                self.h = ctypes.c_void_p()
+        except Exception:  # interpreter shutdown
+            pass
+
+
+class NearestNeighborsMatching(object):
+    """Nearest Neighbor matching of description vectors (reference: nns_matching.py:5)."""
+
+    def __init__(self, dim=None):
+        """Reference: nns_matching.py:9-21."""
+        self.n = 0
+        self.device = torch.device('cuda')
+        self.dim = dim
+        self.items = dict()
+        self._h = None
+        self._view = None
+        self._view_key = None
+        if dim is not None:
+            self._open()
+
+    # -- native handle ---------------------------------------------------------------------------
+    def _device_index(self):
+        dev = torch.device(self.device)
+        if dev.type != 'cuda':
+            raise RuntimeError(
+                "cslam_b200.NearestNeighborsMatching runs on a CUDA device only (device=%s); "
+                "there is no CPU path" % (dev,))
+        return dev.index if dev.index is not None else torch.cuda.current_device()
+
+    def _open(self):
+        if self._h is None:
+            self._h = _Handle(self._device_index(), self.dim)
+        return self._h
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self._device_index()).cuda_stream)
+
+    # -- public attribute `data` (reference: nns_matching.py:19-21, read by tests :36,:49,:66) -----
+    @property
+    def data(self):
+        if self._h is None:
+            return []  # reference: empty python list until the first allocation
+        lib, h = self._h.lib, self._h.h
+        cap, ld, ptr = lib.cslam_nns_capacity(h), lib.cslam_nns_ld(h), lib.cslam_nns_data_ptr(h)
+        key = (cap, ptr)
+        if self._view_key != key:
+            carrier = _CudaArrayView(ptr, (cap, int(self.dim)), (ld * 4, 4), self._h)
+            self._view = torch.as_tensor(carrier, device=torch.device('cuda', lib.cslam_nns_device(h)))
+            self._view_key = key
+        return self._view
+
+    # -- add_item (reference: nns_matching.py:23-42) ------------------------------------------------
+    def add_item(self, vector, item):
+        """Add item to the matching list.
+
+        Args:
+            vector (np.array): descriptor
+            item: identification info (e.g., int)
+        """
+        if not torch.is_tensor(vector):
+            vector = torch.from_numpy(vector.astype(np.float32))
+        if self.dim is None:
+            self.dim = len(vector)
+        h = self._open()
+        row = vector.reshape(1, self.dim)  # RuntimeError on a wrong length, like the reference (:41)
+        row = row.to(torch.float32)
+        self._append(h, row)
+        self.items[self.n] = item
+        self.n += 1
+
+    def add_items(self, matrix, items):
+        """Additive API: append ``len(items)`` rows at once (one DMA instead of one per row)."""
+        if not torch.is_tensor(matrix):
+            matrix = torch.from_numpy(np.asarray(matrix).astype(np.float32))
+        if matrix.dim() != 2:
+            raise ValueError("matrix must be (count, dim)")
+        if self.dim is None:
+            self.dim = int(matrix.shape[1])
+        if matrix.shape[1] != self.dim or matrix.shape[0] != len(items):
+            raise RuntimeError("shape mismatch: matrix %s, dim %s, %d items" %
+                               (tuple(matrix.shape), self.dim, len(items)))
+        h = self._open()
+        self._append(h, matrix.to(torch.float32))
+        for j, item in enumerate(items):
+            self.items[self.n + j] = item
+        self.n += len(items)
+
+    def _append(self, h, rows):
+        rows = rows.contiguous()
+        on_dev = rows.is_cuda
+        if on_dev and rows.device.index != h.lib.cslam_nns_device(h.h):
+            rows = rows.cpu()
+            on_dev = False
+        new_n = ctypes.c_int64()
+        rc = h.lib.cslam_nns_add(h.h, ctypes.c_void_p(rows.data_ptr()), rows.shape[0], rows.shape[1],
+                                 1 if on_dev else 0, self._stream(), ctypes.byref(new_n))
+        _native.check(rc, h.h)
+
+    # -- search (reference: nns_matching.py:44-63) --------------------------------------------------
+    def search(self, query, k):
+        """Search for nearest neighbors.
+
+        Args:
+            query (np.array): descriptor to match
+            k (int): number of best matches to return
+
+        Returns:
+            list(int, np.array): best matches
+        """
+        if self._h is None:  # reference: len(self.data) == 0 -> [], []
+            return [], []
+        if not torch.is_tensor(query):
+            query = torch.from_numpy(query.astype(np.float32))
+        if query.dim() == 2 and not (query.shape[0] == 1 or self.dim == 1):
+            return self.search_batch(query, k)
+        out_dtype = np.float64 if query.dtype == torch.float64 else np.float32  # torch promotion
+        q = query.reshape(1, self.dim).to(torch.float32)
+        idx, sims = self._search_block(q, k)
+        items = [self.items[i] for i in idx[0].tolist()]
+        return items, sims[0].astype(out_dtype, copy=False)
+
+    def search_batch(self, queries, k):
+        """Additive API: ``B`` queries at once -> ``(list of B item lists, sims[B, kk])``."""
+        if self._h is None:
+            return [], []
+        if not torch.is_tensor(queries):
+            queries = torch.from_numpy(np.asarray(queries).astype(np.float32))
+        q = queries.reshape(-1, self.dim).to(torch.float32)
+        idx, sims = self._search_block(q, k)
+        items = [[self.items[i] for i in row] for row in idx.tolist()]
+        return items, sims
+
+    def _search_block(self, q, k):
+        """q: (B, dim) fp32 torch tensor, host or device -> (idx[B,kk] int64, sims[B,kk] f32)."""
+        h = self._h
+        k = int(k)
+        if k < 0:  # python slice semantics of the reference's [:k] for a negative k
+            k = max(self.n + k, 0)
+        kk = min(k, self.n)
+        B = int(q.shape[0])
+        idx = np.empty((B, kk), dtype=np.int64)
+        sims = np.empty((B, kk), dtype=np.float32)
+        if kk == 0 or B == 0:
+            return idx, sims
+        q = q.contiguous()
+        on_dev = q.is_cuda
+        if on_dev and q.device.index != h.lib.cslam_nns_device(h.h):
+            q = q.cpu()
+            on_dev = False
+        rc = h.lib.cslam_nns_search(h.h, ctypes.c_void_p(q.data_ptr()), B, q.shape[1],
+                                    1 if on_dev else 0, kk, ctypes.c_void_p(idx.ctypes.data),
+                                    ctypes.c_void_p(sims.ctypes.data), 0, self._stream(), None)
+        _native.check(rc, h.h)
+        return idx, sims
+
+    # -- search_best (reference: nns_matching.py:65-78) ----------------------------------------------
+    def search_best(self, query):
+        """Search for the nearest neighbor.
+
+        Returns:
+            int, np.array: best match
+        """
+        if self._h is None:
+            return None, None
+        items, similarities = self.search(query, 1)
+        return items[0], similarities[0]

@@ -1,0 +1,137 @@
+/*
+ * cslam_nns.h — C-ABI of the B200-native global-descriptor nearest-neighbour matcher.
+ *
+ * This is the drop-in boundary for ONE hot path of nhahn/cslam:
+ *   cslam/nns_matching.py  NearestNeighborsMatching.{__init__,add_item,search,search_best}
+ * The reference has no FFI for this path (it calls torch/ATen from Python, nns_matching.py:16-63);
+ * the entry points below are what a ctypes binding placed in that file would call
+ * (INTEGRATION.md shows the stub).  Each entry point cites the reference line(s) it replaces.
+ *
+ * Conventions
+ *   - plain C, handle based, no global state; one handle == one descriptor database (one robot's DB),
+ *     exactly like one NearestNeighborsMatching instance (loop_closure_sparse_matching.py:25,32).
+ *   - every function returns 0 on success, a negative CSLAM_NNS_E* code otherwise;
+ *     cslam_nns_last_error(handle) gives the message (handle may be NULL for create-time errors).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  The Python host
+ *     passes torch.cuda.current_stream().cuda_stream.
+ *   - host pointers are ordinary pageable or pinned memory; `*_is_device` says which side a pointer
+ *     lives on.  Calls with host destinations are synchronous on return; calls with device
+ *     destinations are stream-ordered and return immediately.
+ *   - similarities are cosine similarities, fp32, computed as  x.q / (max(|x|,1e-8) * max(|q|,1e-8))
+ *     (torch.nn.functional.cosine_similarity as called at nns_matching.py:61); results are ordered by
+ *     similarity descending (nns_matching.py:62), ties broken by the lower row index, NaN first.
+ *   - row indices are 0-based insertion order (the `self.n` counter of nns_matching.py:40-42).
+ *   - there is NO CPU fallback: every compute entry point fails with CSLAM_NNS_ENODEV when no sm_100
+ *     device is usable.
+ */
+#ifndef CSLAM_NNS_H_
+#define CSLAM_NNS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CSLAM_NNS_OK 0
+#define CSLAM_NNS_EINVAL (-1)   /* bad argument (wrong dim, k<0, NULL pointer, ...) */
+#define CSLAM_NNS_ENODEV (-2)   /* no usable CUDA device / wrong architecture */
+#define CSLAM_NNS_ENOMEM (-3)   /* device or pinned allocation failed, VA reservation exhausted */
+#define CSLAM_NNS_ECUDA (-4)    /* a CUDA runtime/driver call failed; message has the detail */
+#define CSLAM_NNS_ESTATE (-5)   /* call not valid in this state (e.g. search before dim is known) */
+
+typedef struct cslam_nns_s* cslam_nns_t;
+
+/* ABI version of this header (bumped on any signature change). */
+int cslam_nns_abi_version(void);
+
+/* Number of kernels of this library launched so far in this process (all handles). bench.py reads it
+ * before/after the timed region to report `gpu_launches`. */
+int64_t cslam_nns_launch_count(void);
+
+/* Message for the last failing call on `h` (or the last create failure when h == NULL). */
+const char* cslam_nns_last_error(cslam_nns_t h);
+
+/* -- lifetime ----------------------------------------------------------------------------------- */
+
+/* Replaces NearestNeighborsMatching.__init__ (nns_matching.py:9-21).
+ * device: CUDA ordinal.  dim: descriptor size, 0 = decide at first add (the reference's dim=None).
+ * initial_capacity: rows of logical capacity to make available at once (reference: 1000, :21,:36);
+ * <=0 selects 1000.  Capacity doubles like the reference (:38) but growth never copies the DB:
+ * storage is a reserved virtual range into which physical chunks are mapped on demand. */
+int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nns_t* out);
+int cslam_nns_destroy(cslam_nns_t h);
+
+/* Fix the descriptor size of a lazily-dimensioned matcher (nns_matching.py:34-36). */
+int cslam_nns_set_dim(cslam_nns_t h, int64_t dim);
+/* Make room for at least `rows` rows (logical capacity keeps the 1000*2^j sequence). */
+int cslam_nns_reserve(cslam_nns_t h, int64_t rows);
+
+/* -- introspection (backs the public attributes n / dim / data, nns_matching.py:15-21) ---------- */
+int64_t cslam_nns_size(cslam_nns_t h);      /* n */
+int64_t cslam_nns_capacity(cslam_nns_t h);  /* len(self.data) */
+int64_t cslam_nns_dim(cslam_nns_t h);       /* 0 while undecided */
+int64_t cslam_nns_ld(cslam_nns_t h);        /* row pitch in floats (dim rounded up to 4) */
+void* cslam_nns_data_ptr(cslam_nns_t h);    /* device pointer of row 0; stable for the handle's life */
+int cslam_nns_device(cslam_nns_t h);
+
+/* -- add_item (nns_matching.py:23-42) ----------------------------------------------------------- */
+
+/* Append `count` rows of `dim` fp32 values (row pitch src_ld floats, >= dim; 0 means dim).
+ * Stream-ordered; the source buffer may be reused as soon as the call returns.
+ * *new_n (optional) receives the row count after the append. */
+int cslam_nns_add(cslam_nns_t h, const float* rows, int64_t count, int64_t src_ld,
+                  int src_is_device, void* stream, int64_t* new_n);
+
+/* -- search / search_best (nns_matching.py:44-78) ----------------------------------------------- */
+
+/* For each of the B queries (B x dim fp32, pitch q_ld floats, 0 = dim) return the kk = min(k, n)
+ * most similar rows.  out_idx / out_sim are B x k (pitch k); entries [kk, k) of each row are
+ * filled with -1 / -inf.  B == 1 runs the fused single-query kernel (HBM-bound); B >= 2 runs the
+ * tcgen05 3xTF32 batched kernel when k fits its fused epilogue, otherwise one single-query pass per
+ * query.  *out_kk (optional, host) receives kk. */
+int cslam_nns_search(cslam_nns_t h, const float* queries, int64_t B, int64_t q_ld,
+                     int src_is_device, int k, int64_t* out_idx, float* out_sim, int dst_is_device,
+                     void* stream, int64_t* out_kk);
+
+/* -- row-sharded building blocks (no reference counterpart) -------------------------- */
+
+/* Local top-k of this shard as packed 64-bit keys, written to DEVICE memory out_keys[B*k]
+ * (stream-ordered).  key = orderable(sim) << 32 | ~global_row, global_row = local_row*row_stride +
+ * row_offset (striped sharding: stride = world size, offset = rank).  Empty slots hold 0. */
+int cslam_nns_search_keys(cslam_nns_t h, const float* queries, int64_t B, int64_t q_ld,
+                          int src_is_device, int k, int64_t row_stride, int64_t row_offset,
+                          uint64_t* out_keys_dev, void* stream);
+
+/* Merge `parts` key lists per query (keys_dev laid out [parts][B][k], device memory, e.g. the
+ * output of an all-gather of cslam_nns_search_keys results) into the global top-k.
+ * Same output conventions as cslam_nns_search; valid entries per query = number of non-empty keys,
+ * capped at k; *out_kk gets the count for query 0 when the destination is the host. */
+int cslam_nns_merge_keys(int device, const uint64_t* keys_dev, int parts, int64_t B, int k,
+                         int64_t* out_idx, float* out_sim, int dst_is_device, void* stream,
+                         int64_t* out_kk);
+
+/* -- tuning / diagnostics ----------------------------------------------------------------------- */
+
+/* Force a search variant for tests and profiling: 0 = automatic, 1 = single-query kernel looped,
+ * 2 = tcgen05 batched kernel (error if k does not fit), 3 = two-pass (all sims + radix sort). */
+int cslam_nns_set_variant(cslam_nns_t h, int variant);
+/* Variant actually used by the last search on this handle (1, 2 or 3; 0 = none yet). */
+int cslam_nns_last_variant(cslam_nns_t h);
+/* Time in milliseconds (CUDA events on `stream`) of `iters` back-to-back device-resident searches of
+ * the same query block: the kernel-only figure the roofline is computed from.  queries_dev is device
+ * memory; results are discarded.  Returns the per-search average in *ms_per_search. */
+int cslam_nns_time_search(cslam_nns_t h, const float* queries_dev, int64_t B, int64_t q_ld, int k,
+                          int iters, void* stream, float* ms_per_search);
+
+/* Per-kernel timing for the roofline: while enabled, every search on `h` brackets its DOMINANT kernel
+ * (the single-query kernel, or the batched tcgen05 kernel) with CUDA events on the launch stream.
+ * cslam_nns_profile_read synchronises, returns the summed duration of those launches in
+ * milliseconds and their count, and resets the accumulators. */
+int cslam_nns_profile(cslam_nns_t h, int enable);
+int cslam_nns_profile_read(cslam_nns_t h, float* ms_total, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CSLAM_NNS_H_ */

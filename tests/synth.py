@@ -1,0 +1,51 @@
+"""Deterministic synthetic descriptors shared by the golden generator, the tests and bench.py.
+
+A counter-based generator (splitmix64 over the element index) in plain numpy integer arithmetic:
+bit-identical on every machine and numpy version, so fixtures only need to store OUTPUTS.
+"""
+import numpy as np
+
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def _splitmix64(x):
+    x = (x + np.uint64(0x9E3779B97F4A7C15)) & _M64
+    z = x
+    z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & _M64
+    z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & _M64
+    return z ^ (z >> np.uint64(31))
+
+
+def uniform(seed, shape, offset=0):
+    """U[0,1) float64 array; element i depends only on (seed, offset + i)."""
+    n = int(np.prod(shape))
+    with np.errstate(over="ignore"):
+        idx = np.arange(offset, offset + n, dtype=np.uint64)
+        bits = _splitmix64(idx ^ _splitmix64(np.uint64(seed) + np.uint64(0x1234567)))
+    return ((bits >> np.uint64(11)).astype(np.float64) * (1.0 / (1 << 53))).reshape(shape)
+
+
+def normal(seed, shape):
+    """Standard normal via Box-Muller on two uniform streams."""
+    u1 = uniform(seed, shape)
+    u2 = uniform(seed ^ 0x5DEECE66D, shape)
+    return np.sqrt(-2.0 * np.log(1.0 - u1)) * np.cos(2.0 * np.pi * u2)
+
+
+def unit_rows(seed, n, d, dist="rand"):
+    """(n, d) float32 rows, L2-normalised like tests/test_sparse_matching.py:57-58 of the reference."""
+    x = uniform(seed, (n, d)) if dist == "rand" else normal(seed, (n, d))
+    x = x / np.maximum(np.linalg.norm(x, axis=1, keepdims=True), 1e-30)
+    return x.astype(np.float32)
+
+
+def queries_for(seed, db, nq, dist="rand", every=3, noise=0.05):
+    """Queries from the same distribution; every `every`-th one is a noisy copy of a DB row so that
+    true near-duplicates exist."""
+    n, d = db.shape
+    qs = unit_rows(seed, nq, d, dist)
+    eps = normal(seed + 77, (nq, d)).astype(np.float32)
+    for j in range(0, nq, every):
+        v = db[(7 * j + 1) % n] + noise * eps[j]
+        qs[j] = v / np.linalg.norm(v)
+    return qs

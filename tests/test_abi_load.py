@@ -1,0 +1,80 @@
+"""CPU tests of the drop-in boundary: the shared library loads, exports every symbol the header
+declares, and every compute entry point refuses to run without a GPU (no silent fallback)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT
+from cslam_b200 import _native
+
+HAS_GPU = torch.cuda.is_available()
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "cslam_nns.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(cslam_nns_[a-z_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _native.load()
+    declared = _declared_symbols()
+    assert len(declared) >= 18
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert set(declared) == set(_native.SIGNATURES), "ctypes table out of sync with the header"
+    assert lib.cslam_nns_abi_version() == 1
+
+
+def test_library_has_no_libcuda_link_dependency():
+    # the driver API is reached through cudaGetDriverEntryPoint so the .so loads without a driver
+    out = os.popen("ldd %s" % _native.LIB_PATH).read()
+    assert "libcuda.so" not in out and "libtorch" not in out
+
+
+@pytest.mark.skipif(HAS_GPU, reason="checks the no-GPU failure mode")
+def test_create_fails_loudly_without_gpu():
+    lib = _native.load()
+    h = ctypes.c_void_p()
+    rc = lib.cslam_nns_create(0, 16, 0, ctypes.byref(h))
+    assert rc == _native.ENODEV
+    assert not h.value
+    assert b"no CPU fallback" in lib.cslam_nns_last_error(None)
+
+
+@pytest.mark.skipif(HAS_GPU, reason="checks the no-GPU failure mode")
+def test_python_class_fails_loudly_without_gpu():
+    from cslam_b200 import NearestNeighborsMatching
+    m = NearestNeighborsMatching()          # lazy: nothing allocated yet, like the reference
+    assert m.search(np.ones(4), 1) == ([], [])
+    assert m.search_best(np.ones(4)) == (None, None)
+    with pytest.raises(Exception):
+        m.add_item(np.ones(4), 0)           # first allocation needs the device
+    with pytest.raises(Exception):
+        NearestNeighborsMatching(dim=8)
+
+
+def test_reference_api_surface():
+    import inspect
+    from cslam_b200 import NearestNeighborsMatching as M
+    # signatures of cslam/nns_matching.py:9,23,44,65
+    assert list(inspect.signature(M.__init__).parameters) == ["self", "dim"]
+    assert inspect.signature(M.__init__).parameters["dim"].default is None
+    assert list(inspect.signature(M.add_item).parameters) == ["self", "vector", "item"]
+    assert list(inspect.signature(M.search).parameters) == ["self", "query", "k"]
+    assert list(inspect.signature(M.search_best).parameters) == ["self", "query"]
+    m = M()
+    assert (m.n, m.dim, m.items, m.data) == (0, None, {}, [])
+    assert m.device == torch.device("cuda")
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _d, files in os.walk(os.path.join(ROOT, "cslam_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.lower().replace("test infrastructure", ""), f

@@ -1,0 +1,281 @@
+"""GPU parity tests (run with ``-m gpu`` on a B200): the CUDA path, called through the Python
+drop-in and therefore through the C-ABI, against (a) the golden vectors produced by the unmodified
+reference and (b) the CPU oracle on the same seeded inputs.
+
+Parity rule: indices equal to the reference's, except where the reference's own
+neighbouring similarities are closer than the tolerance; similarities within 1e-5*|s| + 1e-6.
+"""
+from collections import namedtuple
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from conftest import case_inputs, config1_inputs
+from oracle import nns_oracle as oracle
+
+pytestmark = pytest.mark.gpu
+RTOL, ATOL = 1e-5, 1e-6
+
+
+@pytest.fixture(scope="module")
+def M():
+    from cslam_b200 import NearestNeighborsMatching
+    return NearestNeighborsMatching
+
+
+def build(M, db, items=None, bulk=False):
+    m = M()
+    if bulk:
+        m.add_items(db, list(range(len(db))) if items is None else items)
+    else:
+        for i, row in enumerate(db):
+            m.add_item(row, i if items is None else items[i])
+    return m
+
+
+def assert_parity(db, q, k, idx, sims):
+    msg = oracle.check_parity(db, q, k, idx, sims, RTOL, ATOL)
+    assert msg is None, msg
+
+
+# ---- golden vectors (reference outputs) -----------------------------------------------------------
+
+def test_golden_search_cases(M, golden_search):
+    for name, c in golden_search.items():
+        db, qs, k = case_inputs(c["spec"])
+        m = build(M, db, items=[1000 + i for i in range(len(db))])
+        assert m.n == len(db) and len(m.data) == int(c["capacity"]), name
+        for j, q in enumerate(qs):
+            items, sims = m.search(q, k)
+            idx = np.asarray(items) - 1000
+            assert sims.dtype == np.float32 and isinstance(items, list)
+            np.testing.assert_allclose(sims, c["sims"][j], rtol=RTOL, atol=ATOL, err_msg=name)
+            assert_parity(db, q, k, idx, sims)
+            # against the reference's own indices, modulo reference ties
+            s64 = oracle.cosine_similarities(db, q, np.float64)
+            for a, b in zip(idx, c["idx"][j]):
+                assert a == b or abs(s64[a] - s64[b]) <= RTOL * abs(s64[b]) + ATOL, (name, j)
+            item, sim = m.search_best(q)
+            assert isinstance(sim, np.float32)
+            assert item == c["best_item"][j] or abs(sim - c["best_sim"][j]) <= ATOL
+            assert abs(sim - c["best_sim"][j]) <= RTOL * abs(c["best_sim"][j]) + ATOL
+
+
+def test_golden_edge_cases(M, golden_edge):
+    g = golden_edge
+    db, qs = g["db"], g["queries"]
+    m = build(M, db)
+    for j, q in enumerate(qs):
+        items, sims = m.search(q, len(db))
+        np.testing.assert_allclose(sims, g["sims"][j], rtol=RTOL, atol=ATOL)
+        assert sorted(items) == list(range(len(db)))
+        assert np.all(sims[:-1] >= sims[1:])
+    # zero row -> 0 similarity; zero query -> all zeros, rows in index order (deterministic ties)
+    items, sims = m.search(qs[2], len(db))
+    assert np.all(sims == 0.0) and items == list(range(len(db)))
+    # float64 torch query -> float64 similarities (torch type promotion in the reference)
+    items, sims = m.search(torch.from_numpy(qs[0].astype(np.float64)), 4)
+    assert sims.dtype == np.float64
+    assert items == g["f64_items"].tolist()
+    np.testing.assert_allclose(sims, g["f64_sims"], rtol=RTOL, atol=ATOL)
+
+
+def test_golden_config1_loop_closure_sparse_matching(golden_config1):
+    """BASELINE config 1: 2 robots x 1k keyframes x 128-d; the candidate-edge set must equal the one
+    the reference produced (keys exactly; weights within tolerance)."""
+    from cslam_b200.loop_closure_sparse_matching import CandidateEdges, LoopClosureSparseMatching
+    GD = namedtuple("GlobalDescriptor", ["keyframe_id", "robot_id", "descriptor"])
+    params = {"robot_id": 0, "max_nb_robots": 2, "frontend.sensor_type": "stereo",
+              "frontend.similarity_threshold": 0.0, "frontend.nb_best_matches": 10,
+              "frontend.intra_loop_min_inbetween_keyframes": 10}
+    local, other = config1_inputs()
+    lcsm = LoopClosureSparseMatching(params, candidate_selector=CandidateEdges(0, 2))
+    intra = []
+    for i in range(len(local)):
+        lcsm.add_local_global_descriptor(local[i], i)
+        kf, _ = lcsm.match_local_loop_closures(local[i], i)
+        intra.append(-1 if kf is None else kf)
+        lcsm.add_other_robot_global_descriptor(GD(i, 1, other[i].tolist()))
+    edges = lcsm.candidate_selector.candidate_edges
+    keys = np.asarray(sorted(edges.keys()), np.int64)
+    g = golden_config1
+    if not np.array_equal(keys, g["edge_keys"]):
+        # any difference must be a tie in the reference's own similarities
+        ours, ref = set(map(tuple, keys.tolist())), set(map(tuple, g["edge_keys"].tolist()))
+        ref_w = {tuple(k): w for k, w in zip(g["edge_keys"].tolist(), g["edge_weights"])}
+        for k in ours - ref:
+            twins = [r for r in ref - ours if (r[0], r[1]) == (k[0], k[1]) or (r[2], r[3]) == (k[2], k[3])]
+            assert twins and min(abs(ref_w[t] - edges[k].weight) for t in twins) <= 2e-6, k
+    else:
+        w = np.asarray([edges[tuple(k)].weight for k in keys.tolist()])
+        np.testing.assert_allclose(w, g["edge_weights"], rtol=RTOL, atol=ATOL)
+    mism = [(a, b) for a, b in zip(intra, g["intra"].tolist()) if a != b]
+    assert len(mism) <= 2, mism[:5]   # only reference-tie cases may differ
+
+
+# ---- oracle on seeded inputs ------------------------------------------------------------------------
+
+@pytest.mark.parametrize("n,d,k,dist", [
+    (1, 8, 1, "rand"), (5, 10, 3, "rand"), (33, 100, 33, "rand"), (1000, 128, 10, "rand"),
+    (1001, 128, 1, "randn"), (4097, 512, 10, "rand"), (3000, 256, 1, "randn"),
+    (2500, 12, 7, "rand"), (300, 2048, 10, "rand"), (130, 4096, 5, "randn"),
+    (64, 9000, 4, "rand"), (20000, 64, 128, "rand"), (777, 36, 100, "randn"),
+])
+def test_single_query_vs_oracle(M, n, d, k, dist):
+    db = synth.unit_rows(100 + n, n, d, dist)
+    qs = synth.queries_for(200 + n, db, 5, dist)
+    m = build(M, db, bulk=True)
+    for q in qs:
+        items, sims = m.search(q, k)
+        assert_parity(db, q, k, np.asarray(items), sims)
+        assert np.all(sims[:-1] >= sims[1:])
+    assert m._h.lib.cslam_nns_last_variant(m._h.h) == 1
+
+
+def test_unnormalised_rows_and_queries(M):
+    db = (synth.uniform(5, (600, 40)) * 7.0 - 2.0).astype(np.float32)
+    q = (synth.uniform(6, (40,)) * 3.0).astype(np.float32)
+    m = build(M, db, bulk=True)
+    items, sims = m.search(q, 10)
+    assert_parity(db, q, 10, np.asarray(items), sims)
+
+
+def test_two_pass_large_k(M):
+    n, d = 5000, 96
+    db = synth.unit_rows(31, n, d)
+    q = synth.unit_rows(32, 1, d)[0]
+    m = build(M, db, bulk=True)
+    for k in (129, 1000, n, n + 50):
+        items, sims = m.search(q, k)
+        assert len(items) == min(k, n)
+        assert_parity(db, q, k, np.asarray(items), sims)
+    assert m._h.lib.cslam_nns_last_variant(m._h.h) == 3
+
+
+def test_batched_matches_single(M):
+    n, d, B, k = 3000, 128, 37, 10
+    db = synth.unit_rows(41, n, d)
+    qs = synth.queries_for(42, db, B)
+    m = build(M, db, bulk=True)
+    items_b, sims_b = m.search_batch(qs, k)
+    assert sims_b.shape == (B, k)
+    for j in range(B):
+        assert_parity(db, qs[j], k, np.asarray(items_b[j]), sims_b[j])
+    # 2-D query through search() takes the batched route as well
+    items2, sims2 = m.search(qs, k)
+    assert items2 == items_b and np.array_equal(sims2, sims_b)
+
+
+def test_device_resident_inputs(M):
+    n, d = 2048, 64
+    db = synth.unit_rows(51, n, d)
+    m = M()
+    m.add_items(torch.from_numpy(db).cuda(), list(range(n)))
+    q = synth.unit_rows(52, 1, d)[0]
+    items, sims = m.search(torch.from_numpy(q).cuda(), 5)
+    assert_parity(db, q, 5, np.asarray(items), sims)
+
+
+# ---- reference semantics (tests/test_sparse_matching.py of the reference) -------------
+
+def test_reference_test_similarity(M):
+    """Same assertions as the reference's test_similarity (tests/test_sparse_matching.py:51-81)."""
+    rng = np.random.default_rng(7)
+    nnsm = M()
+    for i in range(100):
+        v = rng.random(100)
+        nnsm.add_item(v / np.linalg.norm(v), i)
+    for _ in range(100):
+        query = rng.random(100)
+        query = query / np.linalg.norm(query)
+        ds = np.linalg.norm(query[np.newaxis, :] - nnsm.data.cpu().numpy()[:nnsm.n], axis=1)
+        ns_dist = np.argsort(ds)[:100]
+        ns_sim, sims = nnsm.search(query, 100)
+        assert np.all(sims[:-1] >= sims[1:])
+        for j in range(100):
+            id_d, id_s = ns_dist[j], ns_sim[j]
+            if id_d != id_s:
+                if abs(sims[id_d] - sims[id_s]) < 1e-6 or abs(ds[id_d] - ds[id_s]) < 1e-6:
+                    continue
+            assert ns_dist[j] == ns_sim[j]
+        best, _ = nnsm.search_best(query)
+        assert ns_dist[0] == best
+
+
+def test_storage_is_exact_fp32_and_data_view(M):
+    rng = np.random.default_rng(8)
+    m = M()
+    v = rng.random(10)
+    v = v / np.linalg.norm(v)
+    m.add_item(v, "kf-a")                      # items are arbitrary python objects (:40)
+    assert isinstance(m.data, torch.Tensor) and m.data.is_cuda
+    assert tuple(m.data.shape) == (1000, 10) and m.dim == 10 and m.n == 1
+    for i in range(10):                        # reference tests :35-36
+        assert abs(v[i] - float(m.data[0, i])) < 1e-7
+    assert np.array_equal(m.data[0].cpu().numpy(), v.astype(np.float32))
+    assert float(m.data[1:].abs().sum()) == 0.0   # rows past n are zeros, as torch.zeros gives
+    assert m.search_best(v)[0] == "kf-a"
+
+
+def test_capacity_doubles_without_moving_rows(M):
+    d = 20
+    db = synth.unit_rows(61, 4100, d)
+    m = M()
+    caps = set()
+    for i, row in enumerate(db):
+        m.add_item(row, i)
+        caps.add(len(m.data))
+    assert caps == {1000, 2000, 4000, 8000}     # reference sequence (nns_matching.py:36-38)
+    assert np.array_equal(m.data.cpu().numpy()[:m.n], db)
+    items, sims = m.search(db[4099], 1)
+    assert items == [4099] and abs(sims[0] - 1.0) < 1e-6
+
+
+def test_empty_and_quirks(M):
+    m = M()
+    assert m.search(np.ones(4), 3) == ([], []) and m.search_best(np.ones(4)) == (None, None)
+    m2 = M(dim=6)                               # constructed with dim, still empty
+    assert tuple(m2.data.shape) == (1000, 6)
+    items, sims = m2.search(np.ones(6), 3)
+    assert items == [] and sims.shape == (0,) and sims.dtype == np.float32
+    with pytest.raises(IndexError):             # reference quirk
+        m2.search_best(np.ones(6))
+    m2.add_item(np.arange(6, dtype=np.float64), 5)
+    assert m2.search(np.ones(6), 0)[0] == []
+    items, sims = m2.search(np.ones(6), 7)      # k > n -> n results
+    assert items == [5] and sims.shape == (1,)
+    with pytest.raises(RuntimeError):           # wrong length
+        m2.add_item(np.ones(5), 1)
+    with pytest.raises(RuntimeError):
+        m2.search(np.ones(7), 1)
+
+
+def test_nan_row_sorts_first(M):
+    db = synth.unit_rows(71, 50, 8)
+    db[17, 3] = np.nan
+    m = build(M, db, bulk=True)
+    items, sims = m.search(synth.unit_rows(72, 1, 8)[0], 3)
+    assert items[0] == 17 and np.isnan(sims[0])
+
+
+def test_interleaved_add_and_search(M):
+    """Config-4 style: every search must see every earlier add (stream order)."""
+    d = 256
+    db = synth.unit_rows(81, 1500, d)
+    m = M()
+    m.add_items(db[:1000], list(range(1000)))
+    for i in range(1000, 1500):
+        m.add_item(db[i], i)
+        item, sim = m.search_best(db[i])
+        assert item == i and abs(sim - 1.0) < 1e-5
+
+
+def test_no_vmm_fallback_path(M, monkeypatch):
+    monkeypatch.setenv("CSLAM_NNS_NO_VMM", "1")
+    db = synth.unit_rows(91, 2500, 32)
+    m = build(M, db)
+    assert np.array_equal(m.data.cpu().numpy()[:m.n], db)
+    items, sims = m.search(db[2400], 2)
+    assert items[0] == 2400
