@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""Headline benchmark: NN-search queries/s on the configuration BASELINE.json's metric is quoted on.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c4|c5]
+
+Default workload ``c3`` = BASELINE.json configs[2]: 1M x 4096 fp32 descriptors, batches of 256
+queries, top-10 (the "1M x 4096 DB" the metric names).  One *step* = one batch of 256 queries
+searched against the whole database.  With N > 1 ranks (torchrun) the SAME database is row-striped
+over the ranks (strong scaling), every step ends with one all-gather of the B*k packed keys and
+the merge kernel, and timing is the max over ranks of a CUDA-event interval.
+
+The line printed by rank 0 carries, besides the base contract: ``roofline`` (dominant kernel,
+timed live with CUDA events around that kernel only), ``cpu_baseline`` (the C oracle port on the
+host cores, bounded sample), ``e2e`` (same metric through the public Python API with HOST buffers),
+``clocks`` and ``gpu_launches``.
+
+``--impl reference`` times the reference's CPU path for the same metric: the reference is Python +
+torch (cslam/nns_matching.py) and /root/reference does not exist on the benchmark box, so this arm
+runs the oracle port (oracle/nns_oracle.c, one pthread per core) — see DESIGN.md.
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+WORKLOADS = {
+    # name: (rows, dim, batch, k, description)
+    "c3": (1_000_000, 4096, 256, 10, "BASELINE configs[2]: NetVLAD-shaped 1M x 4096 fp32, batch 256, top-10"),
+    "c2": (100_000, 512, 1, 1, "BASELINE configs[1]: CosPlace-shaped 100k x 512 fp32, single query, top-1"),
+    "c4": (2_000_000, 256, 1, 1, "BASELINE configs[3]: 2M x 256 fp32, add_item between single-query top-1 searches"),
+    "c5": (10_000_000, 256, 256, 10, "BASELINE configs[4]: 10M x 256 fp32 row-sharded, batch 256, top-10"),
+}
+METRIC = "NN-search queries/s at 1M×4096 DB; achieved HBM GB/s and fraction of roofline"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override the row count (debugging only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# -------------------------------------------------------------------------------------------------
+# CPU arm (oracle port) — used by cpu_baseline and by --impl reference
+# -------------------------------------------------------------------------------------------------
+
+def cpu_port_qps(rows, dim, batch, k, budget_s=12.0):
+    """Time the C oracle on a bounded row sample of the workload; returns (queries/s scaled to the
+    full row count, cores, description of the sample)."""
+    import numpy as np
+    import subprocess
+    lib_path = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
+    if not os.path.exists(lib_path):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+    lib = ctypes.CDLL(lib_path)
+    lib.oracle_search.restype = ctypes.c_int
+    lib.oracle_search.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64,
+                                  ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p,
+                                  ctypes.c_void_p]
+    lib.oracle_num_threads.restype = ctypes.c_int
+    cores = lib.oracle_num_threads()
+    sample_rows = min(rows, max(1024, (256 << 20) // (dim * 4)))      # <= 256 MB of descriptors
+    rng = np.random.default_rng(3)
+    db = rng.random((sample_rows, dim), dtype=np.float32)
+    db /= np.linalg.norm(db, axis=1, keepdims=True)
+    nq = batch
+    qs = rng.random((nq, dim), dtype=np.float32)
+    idx = np.empty((nq, k), np.int64)
+    sims = np.empty((nq, k), np.float32)
+
+    def run(nquery):
+        t0 = time.perf_counter()
+        lib.oracle_search(db.ctypes.data, sample_rows, dim, dim, qs.ctypes.data, nquery, k,
+                          idx.ctypes.data, sims.ctypes.data)
+        return time.perf_counter() - t0
+
+    run(min(nq, 2))                                   # warm
+    t1 = run(min(nq, 4)) / min(nq, 4)                 # seconds per query on the sample
+    nrun = int(max(1, min(nq, budget_s / max(t1, 1e-9))))
+    t = run(nrun)
+    qps_sample = nrun / t
+    scale = rows / sample_rows
+    desc = ("%d of %d queries over a %d-row sample (1/%.0f of the rows, cost scaled linearly in rows); "
+            "C port of nns_matching.py:57-63, %d pthreads" % (nrun, nq, sample_rows, scale, cores))
+    return qps_sample / scale, cores, desc
+
+
+# -------------------------------------------------------------------------------------------------
+# clocks sampler
+# -------------------------------------------------------------------------------------------------
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                mask = get_reasons(h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+                time.sleep(0.05)
+        except Exception as e:  # pragma: no cover
+            self.reasons.add("sampler_error:%s" % type(e).__name__)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def measured_peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return p["hbm_gbs"], p["bf16_tflops"], p.get("bf16_tflops_sustained", p["bf16_tflops"]), "measured"
+    except Exception:
+        return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+# -------------------------------------------------------------------------------------------------
+def reference_arm(args, rows, dim, batch, k):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    desc, cores = "", 1
+    for i in range(args.warmup + args.steps):
+        qps, cores, desc = cpu_port_qps(rows, dim, batch, k, budget_s=max(2.0, 60.0 / max(1, args.steps + args.warmup)))
+        if i >= args.warmup:
+            vals.append(qps)
+    v = sum(vals) / len(vals)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "queries/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": batch / v * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(args, rows, dim, batch, k),
+            "cpu_baseline": {"value": v, "unit": "queries/s", "cores": cores, "kind": "port", "sample": desc},
+            "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(args, rows, dim, batch, k):
+    return {"workload": WORKLOADS[args.workload][4], "rows": rows, "dim": dim, "batch": batch, "k": k,
+            "sharding": "row-striped over %d rank(s), one all-gather of B*k keys per step" % args.gpus
+            if args.gpus > 1 else "single GPU",
+            "l2": "database (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (rows * dim * 4 / 1e9)}
+
+
+def main():
+    args = parse()
+    rows, dim, batch, k, _ = WORKLOADS[args.workload]
+    if args.rows:
+        rows = args.rows
+    if args.impl == "reference":
+        return reference_arm(args, rows, dim, batch, k)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from cslam_b200 import _native
+    from cslam_b200.sharded import ShardedNearestNeighborsMatching
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
+    lib = _native.load()
+
+    # ---- synthetic database: this rank's stripe, generated on the device in chunks ------------------
+    m = ShardedNearestNeighborsMatching(dim=dim)
+    my_rows = (rows - rank + world - 1) // world
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(3 + 1000 * rank)
+    chunk = max(1, min(my_rows, (1 << 30) // (dim * 4)))
+    done = 0
+    probe = None
+    while done < my_rows:
+        c = min(chunk, my_rows - done)
+        x = torch.rand((c, dim), generator=gen, device=dev, dtype=torch.float32)
+        x /= x.norm(dim=1, keepdim=True)
+        if probe is None:
+            probe = x[: 4 * batch].clone()
+        m.add_local_shard(x)
+        done += c
+        del x
+    m.finalize_bulk()
+    assert m.n == rows
+    # queries: same on every rank; every 10th is a noisy copy of a rank-0 row (true neighbours exist)
+    gq = torch.Generator(device=dev)
+    gq.manual_seed(4)
+    nb = 4
+    queries = torch.rand((nb * batch, dim), generator=gq, device=dev, dtype=torch.float32)
+    if probe.shape[0] >= queries.shape[0]:
+        queries[::10] = probe[: queries.shape[0]][::10] + 0.02 * torch.randn(
+            (queries[::10].shape[0], dim), generator=gq, device=dev)
+    queries /= queries.norm(dim=1, keepdim=True)
+    if world > 1:
+        dist.broadcast(queries, 0)
+    qb = [queries[i * batch:(i + 1) * batch].contiguous() for i in range(nb)]
+    out_idx = torch.empty((batch, k), dtype=torch.int64, device=dev)
+    out_sim = torch.empty((batch, k), dtype=torch.float32, device=dev)
+    h = m.local._h
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident leg: `value` + roofline -----------------------------------------------------
+    for i in range(args.warmup):
+        m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    lib.cslam_nns_profile(h.h, 1)
+    launches0 = lib.cslam_nns_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = lib.cslam_nns_launch_count() - launches0
+    kms, kl = ctypes.c_float(), ctypes.c_int64()
+    lib.cslam_nns_profile_read(h.h, ctypes.byref(kms), ctypes.byref(kl))
+    lib.cslam_nns_profile(h.h, 0)
+    clocks = sampler.stop()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = args.steps * batch / (ms / 1e3)
+    variant = lib.cslam_nns_last_variant(h.h)
+
+    # ---- end-to-end leg: public Python API, host buffers --------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        hq = [torch.from_numpy(q.cpu().numpy()).pin_memory() for q in qb]
+
+        def e2e_step(q_host):
+            if world == 1:   # host queries in, host (rows, sims) out through cslam_nns_search
+                return m.local._search_block(q_host, k)
+            q_dev = q_host.to(dev, non_blocking=True)
+            i_dev, s_dev = m.search_batch_device(q_dev, k)
+            return i_dev.cpu(), s_dev.cpu()
+
+        for i in range(min(args.warmup, 2)):
+            e2e_step(hq[i % nb])
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            e2e_step(hq[i % nb])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": args.steps * batch / float(t.item()), "unit": "queries/s",
+               "h2d_bytes_per_step": batch * dim * 4, "d2h_bytes_per_step": batch * k * 12}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel --------------------------------------------------------------
+    hbm_peak, tf_burst, tf_sust, which = measured_peaks()
+    k_ms = kms.value / max(1, kl.value)
+    local_rows = my_rows
+    if variant == 2:
+        per_launch_q = min(batch, 256)
+        flops = 2.0 * local_rows * dim * per_launch_q
+        achieved = flops / (k_ms / 1e3) / 1e12
+        peak = tf_sust / 2.0
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "frac": achieved / peak, "traffic": None, "kernel": "k2_tcgen05_3xtf32",
+                "issued_frac": 3.0 * achieved / peak, "kernel_ms": k_ms, "launches": kl.value,
+                "note": "achieved = algorithmic 2*N*D*B flops per launch / CUDA-event duration; peak = "
+                        "%s bf16 sustained %.0f TF/s / 2 (tf32 dense is half the bf16 rate); issued_frac "
+                        "counts the 3 tf32 products of the 3xTF32 split" % (which, tf_sust)}
+    else:
+        bytes_ = float(local_rows) * ((dim + 3) // 4 * 4) * 4
+        achieved = bytes_ / (k_ms / 1e3) / 1e9
+        roof = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": None, "kernel": "k1_single_query",
+                "kernel_ms": k_ms, "launches": kl.value,
+                "note": "achieved = N*ld*4 algorithmic bytes per launch / CUDA-event duration; peak = %s "
+                        "copy bandwidth" % which}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        v, cores, desc = cpu_port_qps(rows, dim, batch, k)
+        cpu = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port", "sample": desc}
+
+    line = {"metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products, fp32 accumulate)"
+            if variant == 2 else "f32", "data": "synthetic",
+            "config": dict(workload_config(args, rows, dim, batch, k), search_variant=variant),
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

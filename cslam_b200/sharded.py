@@ -1,0 +1,162 @@
+"""Row-sharded matcher: one process per GPU, one exchange step.
+
+The reference has no multi-GPU path for the matcher; this is the additive scaling layer named by
+BASELINE.json's north_star.  Global row ``i`` lives on rank ``i % world`` as local row ``i // world``
+(striped, so incremental ``add_item`` stays balanced and nothing is ever re-balanced).  A search is
+
+    local top-k on every rank  ->  ONE all_gather of B*k packed 64-bit keys  ->  merge kernel (K4)
+
+The keys carry the global row index and a total order (similarity desc, row asc), so the merged
+result is bit-identical to a single-GPU search of the concatenated database for any world size.
+``torch.distributed`` is the plumbing (NCCL over NVLink on GPUs; the host-side routing logic is
+exercised with gloo in the CPU tests through ``plan_rows`` / ``merge_keys_host``).
+"""
+import ctypes
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _native
+from .nns_matching import NearestNeighborsMatching
+
+
+def plan_rows(first_global_row, count, rank, world):
+    """Which of the ``count`` rows starting at global row ``first_global_row`` belong to ``rank``.
+
+    Returns (positions within the block, their local row numbers)."""
+    g = np.arange(first_global_row, first_global_row + count, dtype=np.int64)
+    mine = np.nonzero(g % world == rank)[0]
+    return mine, g[mine] // world
+
+
+def merge_keys_host(keys, k):
+    """Host restatement of the K4 merge on packed keys (used by the gloo tests): keys is an integer
+    array [parts, B, k] of uint64 keys; returns (global_rows[B, kk], sims[B, kk])."""
+    keys = np.asarray(keys, dtype=np.uint64)
+    parts, B, kin = keys.shape
+    flat = np.transpose(keys, (1, 0, 2)).reshape(B, parts * kin)
+    order = np.argsort(flat, axis=1, kind="stable")[:, ::-1][:, :k]
+    top = np.take_along_axis(flat, order, axis=1)
+    valid = top != 0
+    rows = (~top & np.uint64(0xFFFFFFFF)).astype(np.int64)
+    ordk = (top >> np.uint64(32)).astype(np.uint32)
+    neg = (ordk & np.uint32(0x80000000)) == 0
+    bits = np.where(neg, ~ordk, ordk & np.uint32(0x7FFFFFFF)).astype(np.uint32)
+    sims = bits.view(np.float32)
+    rows = np.where(valid, rows, -1)
+    sims = np.where(valid, sims, -np.inf).astype(np.float32)
+    return rows, sims
+
+
+class ShardedNearestNeighborsMatching(object):
+    """Same three methods as the reference matcher; every rank calls them with the same arguments."""
+
+    def __init__(self, dim=None, group=None):
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.local = NearestNeighborsMatching(dim)
+        self.n = 0            # global row count
+        self.items = dict()   # global row -> item (kept on every rank; tiny)
+        self.dim = dim
+
+    def add_item(self, vector, item):
+        if self.dim is None:
+            self.dim = len(vector)
+        if self.n % self.world == self.rank:
+            self.local.add_item(vector, self.n)
+        self.items[self.n] = item
+        self.n += 1
+
+    def add_items(self, matrix, items):
+        if self.dim is None:
+            self.dim = int(matrix.shape[1])
+        mine, _local = plan_rows(self.n, len(items), self.rank, self.world)
+        if len(mine):
+            sel = matrix[torch.as_tensor(mine, device=matrix.device)] if torch.is_tensor(matrix) \
+                else np.asarray(matrix)[mine]
+            self.local.add_items(sel, [self.n + int(j) for j in mine])
+        for j, item in enumerate(items):
+            self.items[self.n + j] = item
+        self.n += len(items)
+
+    def add_local_shard(self, matrix_dev):
+        """Bulk-load rows that are ALREADY this rank's shard (benchmarks build shards in place).
+        Local row j is global row j*world + rank.  No per-row python bookkeeping: results of the
+        device-level search are global row numbers."""
+        if self.local.dim is None:
+            self.local.dim = int(matrix_dev.shape[1])
+            self.dim = self.local.dim
+        h = self.local._open()
+        self.local._append(h, matrix_dev.to(torch.float32))
+        self.local.n += int(matrix_dev.shape[0])
+
+    def finalize_bulk(self):
+        """After add_local_shard on every rank: agree on the global row count."""
+        t = torch.tensor([self.local.n], dtype=torch.int64, device="cuda")
+        if self.world > 1:
+            dist.all_reduce(t, group=self.group)
+        self.n = int(t.item())
+
+    # -- search ------------------------------------------------------------------------------------
+    def search_keys_device(self, q_dev, k):
+        """Local top-k as packed keys (device int64 tensor [B, k]); stream-ordered, no sync."""
+        if self.local.dim is None and self.dim is not None:
+            self.local.dim = self.dim  # this rank owns no row yet
+        h = self.local._open() if self.local.dim is not None else None
+        B = int(q_dev.shape[0])
+        keys = torch.zeros((B, k), dtype=torch.int64, device=q_dev.device)
+        if h is None or self.local.n == 0:
+            return keys
+        rc = h.lib.cslam_nns_search_keys(h.h, ctypes.c_void_p(q_dev.data_ptr()), B, q_dev.shape[1], 1,
+                                         k, self.world, self.rank, ctypes.c_void_p(keys.data_ptr()),
+                                         self.local._stream())
+        _native.check(rc, h.h)
+        return keys
+
+    def search_batch_device(self, q_dev, k, out_idx=None, out_sim=None):
+        """Device in, device out: (global rows int64 [B,k], sims f32 [B,k]); -1/-inf past the end."""
+        q_dev = q_dev.contiguous()
+        B = int(q_dev.shape[0])
+        keys = self.search_keys_device(q_dev, k)
+        if self.world > 1:
+            gathered = torch.empty((self.world, B, k), dtype=torch.int64, device=q_dev.device)
+            dist.all_gather_into_tensor(gathered, keys, group=self.group)
+        else:
+            gathered = keys.view(1, B, k)
+        if out_idx is None:
+            out_idx = torch.empty((B, k), dtype=torch.int64, device=q_dev.device)
+            out_sim = torch.empty((B, k), dtype=torch.float32, device=q_dev.device)
+        lib = _native.load()
+        rc = lib.cslam_nns_merge_keys(q_dev.device.index, ctypes.c_void_p(gathered.data_ptr()),
+                                      self.world, B, k, ctypes.c_void_p(out_idx.data_ptr()),
+                                      ctypes.c_void_p(out_sim.data_ptr()), 1,
+                                      ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), None)
+        _native.check(rc, None)
+        return out_idx, out_sim
+
+    def search_batch(self, queries, k):
+        if not torch.is_tensor(queries):
+            queries = torch.from_numpy(np.asarray(queries).astype(np.float32))
+        k = int(k)
+        kk = min(k, self.n)
+        B = int(queries.reshape(-1, self.dim).shape[0]) if self.dim else 0
+        if kk == 0 or B == 0:
+            return [[] for _ in range(B)], np.empty((B, 0), np.float32)
+        q = queries.reshape(-1, self.dim).to(torch.float32).cuda(non_blocking=True)
+        idx, sims = self.search_batch_device(q, kk)
+        idx, sims = idx.cpu().numpy(), sims.cpu().numpy()
+        return [[self.items[i] for i in row] for row in idx.tolist()], sims
+
+    def search(self, query, k):
+        if self.n == 0 and self.dim is None:
+            return [], []
+        items, sims = self.search_batch(query, k)
+        return items[0], sims[0]
+
+    def search_best(self, query):
+        if self.n == 0 and self.dim is None:
+            return None, None
+        items, sims = self.search(query, 1)
+        return items[0], sims[0]
