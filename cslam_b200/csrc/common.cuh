@@ -105,6 +105,20 @@ __device__ __forceinline__ void warp_list_stream(u64* list, int k, u64& thr, con
   }
 }
 
+// Block-wide exact select: out[r] = the candidate with exactly r larger candidates, for r < k.
+// Keys are unique (they embed the row) except for empties (0), which are skipped.  `out[0..k)` must be
+// zeroed and visible to the block before the call; all threads of the block call it.  O(M^2 / threads)
+// comparisons: meant for the small candidate sets of the merge steps.
+__device__ __forceinline__ void block_rank_select(const u64* cand, int M, int k, u64* out) {
+  for (int i = threadIdx.x; i < M; i += blockDim.x) {
+    const u64 key = cand[i];
+    if (key == 0ull) continue;
+    int rank = 0;
+    for (int j = 0; j < M; ++j) rank += (cand[j] > key) ? 1 : 0;
+    if (rank < k) out[rank] = key;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // PTX wrappers: mbarrier, bulk async copy (TMA 1-D), TMA 2-D tiles, tcgen05.
 // ------------------------------------------------------------------------------------------------

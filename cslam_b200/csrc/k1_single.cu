@@ -68,11 +68,54 @@ __device__ __forceinline__ float group_sum(float v, int lpr) {
   return v;
 }
 
-__device__ __forceinline__ float cos_from(float dot, float nn, float qn) {
-  // x.q / (max(|x|,eps) * max(|q|,eps)), nns_matching.py:61
-  return dot / (fmaxf(sqrtf(nn), kEps) * qn);
+
+// sim = x.q / (max(|x|,eps) * max(|q|,eps)) with one MUFU.RSQ: max(sqrt(nn),eps) == sqrt(max(nn,eps^2))
+__device__ __forceinline__ float cos_fast(float dot, float nn, float inv_qn) {
+  return dot * rsqrtf(fmaxf(nn, kEps * kEps)) * inv_qn;
 }
 
+// Per-warp running top-k.  k == 1: the best key is the register `thr`.  k <= 32: lane j holds the
+// j-th best key in `mine` (sorted descending, 0 = empty).  k > 32: sorted list in shared memory.
+__device__ __forceinline__ void offer(u64* list, int k, u64 key, bool have, u64& thr, u64& mine,
+                                      int lane) {
+  unsigned m = __ballot_sync(kFull, have && key > thr);
+  if (m == 0) return;  // the common case after warm-up
+  if (k == 1) {
+    u64 best = (have && key > thr) ? key : 0ull;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const u64 o = __shfl_xor_sync(kFull, best, off);
+      best = o > best ? o : best;
+    }
+    thr = best;  // best > old thr by construction
+  } else if (k <= 32) {
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const u64 cand = __shfl_sync(kFull, key, src);
+      if (cand > thr) {
+        const int pos = __popc(__ballot_sync(kFull, lane < k && mine > cand));
+        const u64 up = __shfl_up_sync(kFull, mine, 1);
+        if (lane < k) {
+          if (lane > pos) mine = up;
+          else if (lane == pos) mine = cand;
+        }
+        thr = __shfl_sync(kFull, mine, k - 1);
+      }
+    }
+  } else {
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      warp_list_insert(list, k, __shfl_sync(kFull, key, src), thr, lane);
+    }
+  }
+}
+
+// NQ > 0: the query lives in registers (NQ float4 per lane), rows are whole inside one tile.
+// NQ == 0: rows longer than a stage; the query is staged in shared memory and a row is accumulated
+//          across column chunks.
+template <int NQ>
 __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -80,9 +123,10 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
 
   unsigned char* stage_base = smem;
   float4* q_s = reinterpret_cast<float4*>(smem + (size_t)W * S * p.stage_bytes);
-  u64* lists = reinterpret_cast<u64*>(reinterpret_cast<unsigned char*>(q_s) + (size_t)p.ld4 * 16);
+  u64* lists = reinterpret_cast<u64*>(reinterpret_cast<unsigned char*>(q_s) +
+                                      (NQ == 0 ? (size_t)p.ld4 * 16 : 0));
   uint64_t* bars = reinterpret_cast<uint64_t*>(lists + (size_t)W * p.k);
-  float* red = reinterpret_cast<float*>(bars + W * S);  // [W] partial |q|^2, then [W] = qn
+  float* red = reinterpret_cast<float*>(bars + W * S);
   int* flag = reinterpret_cast<int*>(red + W + 1);
 
   const long long GW = (long long)gridDim.x * W;
@@ -102,7 +146,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     const long long row0 = (gw + tj * GW) * R;
     const float4* src;
     uint32_t bytes;
-    if (p.n_chunks == 1) {
+    if (NQ > 0) {
       long long rows = p.n - row0;
       if (rows > R) rows = R;
       src = p.db + row0 * p.ld4;
@@ -124,85 +168,72 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     fence_proxy_async();
     for (int i = 0; i < S && i < my_items; ++i) issue(i);
   }
-
-  // -- stage the query, compute max(|q|, eps) ----------------------------------------------------
-  {
-    float* qf = reinterpret_cast<float*>(q_s);
-    float part = 0.f;
-    for (int i = tid; i < p.ld4 * 4; i += W * 32) {
-      float v = i < p.dim ? p.q[i] : 0.f;
-      qf[i] = v;
-      part = fmaf(v, v, part);
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) part += __shfl_xor_sync(kFull, part, off);
-    if (lane == 0) red[warp] = part;
-    u64* my_list0 = lists + (size_t)warp * p.k;
-    warp_list_clear(my_list0, p.k, lane);
-    __syncthreads();
-    if (tid == 0) {
-      float t = 0.f;
-      for (int w = 0; w < W; ++w) t += red[w];
-      red[W] = fmaxf(sqrtf(t), kEps);
-    }
-    __syncthreads();
-  }
-  const float qn = red[W];
   u64* my_list = lists + (size_t)warp * p.k;
-  u64 thr = 0ull;
+  if (p.k > 32) warp_list_clear(my_list, p.k, lane);
+  u64 thr = 0ull, mine = 0ull;
 
   const int lpr = 1 << p.lpr_log2;
   const int G = 32 >> p.lpr_log2;
   const int sub = lane & (lpr - 1);
   const int grp = lane >> p.lpr_log2;
 
-  // -- stream the DB ----------------------------------------------------------------------------
-  if (p.n_chunks == 1) {
+  if (NQ > 0) {
+    // -- query into registers: lane holds q4[sub + i*lpr]; every lane group covers q once ---------
+    float4 qreg[NQ > 0 ? NQ : 1];
+    float part = 0.f;
+#pragma unroll
+    for (int i = 0; i < NQ; ++i) {
+      const int j = sub + i * lpr;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (j < p.ld4) {
+        if (4 * j + 3 < p.dim) {
+          v = __ldg(reinterpret_cast<const float4*>(p.q) + j);
+        } else {  // last, partial float4 of a dim that is not a multiple of 4
+          if (4 * j + 0 < p.dim) v.x = __ldg(p.q + 4 * j + 0);
+          if (4 * j + 1 < p.dim) v.y = __ldg(p.q + 4 * j + 1);
+          if (4 * j + 2 < p.dim) v.z = __ldg(p.q + 4 * j + 2);
+        }
+      }
+      qreg[i] = v;
+      part = fmaf(v.x, v.x, part);
+      part = fmaf(v.y, v.y, part);
+      part = fmaf(v.z, v.z, part);
+      part = fmaf(v.w, v.w, part);
+    }
+    part = group_sum(part, lpr);
+    const float inv_qn = 1.0f / fmaxf(sqrtf(part), kEps);
+
     for (long long it = 0; it < my_items; ++it) {
       const int s = (int)(it % S);
       const uint32_t parity = (uint32_t)((it / S) & 1);
       const long long row0 = (gw + it * GW) * R;
-      long long rows_ll = p.n - row0;
+      const long long rows_ll = p.n - row0;
       const int rows = rows_ll > R ? R : (int)rows_ll;
       mbar_wait(&my_bars[s], parity);
       const float4* buf = reinterpret_cast<const float4*>(my_stage + (size_t)s * p.stage_bytes);
-
-      for (int r0 = 0; r0 < rows; r0 += G * U) {
-        float dot[U], nn[U];
-        int rr[U];
-        const float4* rowp[U];
+      for (int r0 = 0; r0 < rows; r0 += G) {
+        const int rr = r0 + grp;
+        const int rc = rr < rows ? rr : rows - 1;
+        const float4* rowp = buf + (size_t)rc * p.ld4 + sub;
+        float4 x[NQ > 0 ? NQ : 1];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          dot[u] = 0.f;
-          nn[u] = 0.f;
-          rr[u] = r0 + u * G + grp;
-          int rc = rr[u] < rows ? rr[u] : rows - 1;
-          rowp[u] = buf + (size_t)rc * p.ld4;
+        for (int i = 0; i < NQ; ++i)
+          x[i] = (sub + i * lpr < p.ld4) ? rowp[i * lpr] : make_float4(0.f, 0.f, 0.f, 0.f);
+        float d0 = 0.f, n0 = 0.f, d1 = 0.f, n1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < NQ; ++i) {
+          if (i & 1) fma4(x[i], qreg[i], d1, n1);
+          else fma4(x[i], qreg[i], d0, n0);
         }
-#pragma unroll 2
-        for (int j = sub; j < p.ld4; j += lpr) {
-          const float4 qv = q_s[j];
-          float4 x[U];
-#pragma unroll
-          for (int u = 0; u < U; ++u) x[u] = rowp[u][j];
-#pragma unroll
-          for (int u = 0; u < U; ++u) fma4(x[u], qv, dot[u], nn[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          dot[u] = group_sum(dot[u], lpr);
-          nn[u] = group_sum(nn[u], lpr);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const bool valid = (rr[u] < rows) && (sub == 0);
-          const float s_ = cos_from(dot[u], nn[u], qn);
-          const long long row = row0 + rr[u];
-          if (p.all_sims) {
-            if (valid) p.all_sims[row] = s_;
-          } else {
-            warp_list_offer(my_list, p.k, make_key(s_, (uint32_t)row), valid, thr, lane);
-          }
+        const float dot = group_sum(d0 + d1, lpr);
+        const float nn = group_sum(n0 + n1, lpr);
+        const float s_ = cos_fast(dot, nn, inv_qn);
+        const bool valid = (rr < rows) && (sub == 0);
+        const long long row = row0 + rr;
+        if (p.all_sims) {
+          if (valid) p.all_sims[row] = s_;
+        } else {
+          offer(my_list, p.k, make_key(s_, (uint32_t)row), valid, thr, mine, lane);
         }
       }
       __syncwarp();
@@ -212,7 +243,26 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       }
     }
   } else {
-    // rows longer than one stage: accumulate across column chunks (one row per tile, LPR = 32)
+    // -- stage the query in shared memory, compute 1/max(|q|, eps) --------------------------------
+    float* qf = reinterpret_cast<float*>(q_s);
+    float part = 0.f;
+    for (int i = tid; i < p.ld4 * 4; i += W * 32) {
+      const float v = i < p.dim ? p.q[i] : 0.f;
+      qf[i] = v;
+      part = fmaf(v, v, part);
+    }
+    part = group_sum(part, 32);
+    if (lane == 0) red[warp] = part;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int w = 0; w < W; ++w) t += red[w];
+      red[W] = 1.0f / fmaxf(sqrtf(t), kEps);
+    }
+    __syncthreads();
+    const float inv_qn = red[W];
+
+    // one row per tile, accumulated across column chunks by the whole warp
     float dot = 0.f, nn = 0.f;
     for (long long it = 0; it < my_items; ++it) {
       const int s = (int)(it % S);
@@ -228,8 +278,8 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       float d0 = 0.f, n0 = 0.f, d1 = 0.f, n1 = 0.f;
       int j = lane;
       for (; j + 32 < f4; j += 64) {
-        float4 x0 = buf[j], x1 = buf[j + 32];
-        float4 q0 = qc[j], q1 = qc[j + 32];
+        const float4 x0 = buf[j], x1 = buf[j + 32];
+        const float4 q0 = qc[j], q1 = qc[j + 32];
         fma4(x0, q0, d0, n0);
         fma4(x1, q1, d1, n1);
       }
@@ -239,11 +289,11 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       if (c == p.n_chunks - 1) {
         dot = group_sum(dot, 32);
         nn = group_sum(nn, 32);
-        const float s_ = cos_from(dot, nn, qn);
+        const float s_ = cos_fast(dot, nn, inv_qn);
         if (p.all_sims) {
           if (lane == 0) p.all_sims[row] = s_;
         } else {
-          warp_list_offer(my_list, p.k, make_key(s_, (uint32_t)row), lane == 0, thr, lane);
+          offer(my_list, p.k, make_key(s_, (uint32_t)row), lane == 0, thr, mine, lane);
         }
         dot = 0.f;
         nn = 0.f;
@@ -258,49 +308,65 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   if (p.all_sims) return;
 
   // -- CTA merge -> scratch ---------------------------------------------------------------------
+  u64* cta_out = reinterpret_cast<u64*>((reinterpret_cast<uintptr_t>(flag + 2) + 7) & ~(uintptr_t)7);  // [k]
+  if (p.k == 1) {
+    if (lane == 0) my_list[0] = thr;
+  } else if (p.k <= 32) {
+    if (lane < p.k) my_list[lane] = mine;
+  }
+  for (int i = tid; i < p.k; i += W * 32) cta_out[i] = 0ull;
   __syncthreads();
-  if (warp == 0) {
-    for (int w = 1; w < W; ++w) warp_list_stream(my_list, p.k, thr, lists + (size_t)w * p.k, p.k, lane);
-    for (int i = lane; i < p.k; i += 32) p.scratch[(size_t)blockIdx.x * p.k + i] = my_list[i];
-    __threadfence();
-    __syncwarp();
-    if (lane == 0) {
-      unsigned t = atomicAdd(p.ticket, 1u);
-      *flag = (t == gridDim.x - 1);
-    }
+  block_rank_select(lists, W * p.k, p.k, cta_out);
+  __syncthreads();
+  for (int i = tid; i < p.k; i += W * 32) p.scratch[(size_t)blockIdx.x * p.k + i] = cta_out[i];
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned t = atomicAdd(p.ticket, 1u);
+    *flag = (t == gridDim.x - 1);
   }
   __syncthreads();
   if (!*flag) return;
 
-  // -- last CTA: merge the grid's lists, decode, publish ------------------------------------------
+  // -- last CTA: prune with tau = the best k-th key of any CTA (k candidates >= tau exist, so nothing
+  //    below it can be in the top-k), rank-select the survivors, decode, publish -------------------
   __threadfence();
-  const long long total = (long long)gridDim.x * p.k;
-  const long long per = (total + W - 1) / W;
-  warp_list_clear(my_list, p.k, lane);
-  thr = 0ull;
-  {
-    long long lo = per * warp, hi = lo + per;
-    if (hi > total) hi = total;
-    for (long long base = lo; base < hi; base += 32) {
-      long long i = base + lane;
-      u64 key = 0ull;
-      if (i < hi) key = __ldcg(p.scratch + i);
-      warp_list_offer(my_list, p.k, key, key != 0ull, thr, lane);
-    }
+  u64* surv = reinterpret_cast<u64*>(smem);  // the ring is idle now: every issued copy was consumed
+  int* cnt = flag + 1;
+  u64 tau = 0ull;
+  for (int c = tid; c < (int)gridDim.x; c += W * 32) {
+    const u64 v = __ldcg(p.scratch + (size_t)c * p.k + (p.k - 1));
+    tau = v > tau ? v : tau;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const u64 o = __shfl_xor_sync(kFull, tau, off);
+    tau = o > tau ? o : tau;
+  }
+  u64* red64 = reinterpret_cast<u64*>(bars);  // barriers are dead as well
+  if (lane == 0) red64[warp] = tau;
+  if (tid == 0) *cnt = 0;
+  for (int i = tid; i < p.k; i += W * 32) cta_out[i] = 0ull;
+  __syncthreads();
+  tau = 0ull;
+  for (int w = 0; w < W; ++w) tau = red64[w] > tau ? red64[w] : tau;
+  const int total = (int)gridDim.x * p.k;
+  for (int i = tid; i < total; i += W * 32) {
+    const u64 key = __ldcg(p.scratch + i);
+    if (key != 0ull && key >= tau) surv[atomicAdd(cnt, 1)] = key;
   }
   __syncthreads();
-  if (warp == 0) {
-    for (int w = 1; w < W; ++w) warp_list_stream(my_list, p.k, thr, lists + (size_t)w * p.k, p.k, lane);
-    for (int i = lane; i < p.k; i += 32) {
-      const u64 key = my_list[i];
-      const bool have = key != 0ull;
-      const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
-      if (p.out_keys) p.out_keys[i] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
-      if (p.out_idx) p.out_idx[i] = have ? grow : -1ll;
-      if (p.out_sim) p.out_sim[i] = have ? key_sim(key) : -INFINITY;
-    }
-    if (lane == 0) *p.ticket = 0u;
+  block_rank_select(surv, *cnt, p.k, cta_out);
+  __syncthreads();
+  for (int i = tid; i < p.k; i += W * 32) {
+    const u64 key = cta_out[i];
+    const bool have = key != 0ull;
+    const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
+    if (p.out_keys) p.out_keys[i] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
+    if (p.out_idx) p.out_idx[i] = have ? grow : -1ll;
+    if (p.out_sim) p.out_sim[i] = have ? key_sim(key) : -INFINITY;
   }
+  if (tid == 0) *p.ticket = 0u;
 }
 
 inline int ceil_log2(int v) {
@@ -331,33 +397,46 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   p.all_sims = a.all_sims;
 
   const long long row_bytes = (long long)a.ld * 4;
-  // query + per-warp lists + mbarriers (<= 16 stages) + reduction scratch
-  const size_t fixed = (size_t)p.ld4 * 16 + (size_t)W * a.k * 8 + (size_t)W * 16 * 8 + 128;
   const size_t smem_cap = 227 * 1024;
   int stages = t.stages < 2 ? 2 : (t.stages > 16 ? 16 : t.stages);
   long long target = t.stage_bytes < 512 ? 512 : t.stage_bytes;
   target &= ~15ll;
-  // shrink the ring until it fits beside the query and the lists
+
+  // lanes per row: 8 by default (a quarter-warp reads 128 contiguous bytes), fewer for tiny rows,
+  // more when a lane would otherwise need more than 16 query float4 in registers
+  int lpr = 8;
+  while (lpr > 1 && lpr / 2 >= p.ld4) lpr /= 2;
+  while ((p.ld4 + lpr - 1) / lpr > 16 && lpr < 32) lpr *= 2;
+  int nq = (p.ld4 + lpr - 1) / lpr;
+  const bool reg_path = row_bytes <= target && nq <= 16;
+
+  // mbarriers (<= 16 stages) + reduction scratch + per-warp lists (+ the query on the chunked path)
+  const size_t fixed = (size_t)W * a.k * 8 + (size_t)W * 16 * 8 + 128 + (size_t)a.k * 8 +
+                       (reg_path ? 0 : (size_t)p.ld4 * 16);
   while ((size_t)W * stages * target + fixed > smem_cap) {
     if (stages > 2) --stages;
     else if (target > 1024) target = (target / 2) & ~15ll;
     else return cudaErrorInvalidConfiguration;
   }
-  if (row_bytes <= target) {
+  int NQ = 0;
+  if (reg_path && row_bytes <= target) {
     p.rows_per_tile = (int)(target / row_bytes);
+    const int G = 32 / lpr;
+    if (p.rows_per_tile > G) p.rows_per_tile = p.rows_per_tile / G * G;  // whole passes
     p.n_chunks = 1;
     p.chunk_f4 = p.ld4;
     p.stage_bytes = (int)(((long long)p.rows_per_tile * row_bytes + 127) & ~127ll);
+    NQ = nq <= 4 ? 4 : (nq <= 8 ? 8 : 16);
   } else {
     p.rows_per_tile = 1;
     p.chunk_f4 = (int)(target / 16);
+    if (p.chunk_f4 > p.ld4) p.chunk_f4 = p.ld4;
     p.n_chunks = (p.ld4 + p.chunk_f4 - 1) / p.chunk_f4;
-    p.stage_bytes = (int)((target + 127) & ~127ll);
+    p.stage_bytes = (int)(((long long)p.chunk_f4 * 16 + 127) & ~127ll);
+    lpr = 32;
   }
   p.stages = stages;
-  p.lpr_log2 = ceil_log2(p.ld4);
-  if (p.lpr_log2 > 5) p.lpr_log2 = 5;
-  if (p.n_chunks > 1) p.lpr_log2 = 5;
+  p.lpr_log2 = ceil_log2(lpr);
 
   const long long tiles = (a.n + p.rows_per_tile - 1) / p.rows_per_tile;
   long long grid = (tiles + W - 1) / W;
@@ -366,17 +445,29 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
 
+  // the last CTA re-uses the ring as the survivor buffer of the final merge: grid * k keys
+  while (grid > 1 && (size_t)grid * a.k * 8 > (size_t)W * p.stages * p.stage_bytes) --grid;
+  if ((size_t)grid * a.k * 8 > (size_t)W * p.stages * p.stage_bytes) return cudaErrorInvalidConfiguration;
   const size_t smem = (size_t)W * p.stages * p.stage_bytes + fixed;
   static bool attr_set[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(k1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem_cap);
+    cudaError_t e = cudaSuccess;
+    e = cudaFuncSetAttribute(k1_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  k1_kernel<<<(unsigned)grid, W * 32, smem, stream>>>(p);
+  const dim3 g((unsigned)grid), b(W * 32);
+  switch (NQ) {
+    case 4: k1_kernel<4><<<g, b, smem, stream>>>(p); break;
+    case 8: k1_kernel<8><<<g, b, smem, stream>>>(p); break;
+    case 16: k1_kernel<16><<<g, b, smem, stream>>>(p); break;
+    default: k1_kernel<0><<<g, b, smem, stream>>>(p); break;
+  }
   count_launch();
   return cudaGetLastError();
 }
