@@ -333,23 +333,36 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   __threadfence();
   u64* surv = reinterpret_cast<u64*>(smem);  // the ring is idle now: every issued copy was consumed
   int* cnt = flag + 1;
-  u64 tau = 0ull;
-  for (int c = tid; c < (int)gridDim.x; c += W * 32) {
-    const u64 v = __ldcg(p.scratch + (size_t)c * p.k + (p.k - 1));
-    tau = v > tau ? v : tau;
+  // tau: a lower bound of the global k-th key.  For a list position j, the m-th largest of the
+  // grid's j-th entries has at least m*(j+1) >= k keys at or above it when m = ceil(k/(j+1)).
+  // Try j+1 = 1, 2, 4, ... and j = k-1; keep the largest bound.
+  const int Gd = (int)gridDim.x;
+  u64* col = surv + (size_t)Gd * p.k;  // [grid] scratch column, behind the survivor buffer
+  u64* red64 = reinterpret_cast<u64*>(bars);  // barriers are dead as well: [0] = tau
+  if (tid == 0) {
+    red64[0] = 0ull;
+    *cnt = 0;
   }
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    const u64 o = __shfl_xor_sync(kFull, tau, off);
-    tau = o > tau ? o : tau;
-  }
-  u64* red64 = reinterpret_cast<u64*>(bars);  // barriers are dead as well
-  if (lane == 0) red64[warp] = tau;
-  if (tid == 0) *cnt = 0;
   for (int i = tid; i < p.k; i += W * 32) cta_out[i] = 0ull;
   __syncthreads();
-  tau = 0ull;
-  for (int w = 0; w < W; ++w) tau = red64[w] > tau ? red64[w] : tau;
+  for (int jp1 = 1;; jp1 *= 2) {
+    if (jp1 > p.k) jp1 = p.k;
+    const int m = (p.k + jp1 - 1) / jp1;
+    if (m <= Gd) {
+      for (int c = tid; c < Gd; c += W * 32) col[c] = __ldcg(p.scratch + (size_t)c * p.k + (jp1 - 1));
+      __syncthreads();
+      for (int c = tid; c < Gd; c += W * 32) {
+        const u64 v = col[c];
+        if (v == 0ull) continue;
+        int rank = 0;
+        for (int j = 0; j < Gd; ++j) rank += (col[j] > v) ? 1 : 0;
+        if (rank == m - 1) atomicMax(&red64[0], v);
+      }
+      __syncthreads();
+    }
+    if (jp1 == p.k) break;
+  }
+  const u64 tau = red64[0];
   const int total = (int)gridDim.x * p.k;
   for (int i = tid; i < total; i += W * 32) {
     const u64 key = __ldcg(p.scratch + i);
@@ -446,8 +459,8 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   if (grid < 1) grid = 1;
 
   // the last CTA re-uses the ring as the survivor buffer of the final merge: grid * k keys
-  while (grid > 1 && (size_t)grid * a.k * 8 > (size_t)W * p.stages * p.stage_bytes) --grid;
-  if ((size_t)grid * a.k * 8 > (size_t)W * p.stages * p.stage_bytes) return cudaErrorInvalidConfiguration;
+  while (grid > 1 && (size_t)grid * (a.k + 1) * 8 > (size_t)W * p.stages * p.stage_bytes) --grid;
+  if ((size_t)grid * (a.k + 1) * 8 > (size_t)W * p.stages * p.stage_bytes) return cudaErrorInvalidConfiguration;
   const size_t smem = (size_t)W * p.stages * p.stage_bytes + fixed;
   static bool attr_set[64] = {};
   int dev = 0;
