@@ -1,9 +1,468 @@
-// placeholder — replaced by the tcgen05 kernel
+// K2 — batched cosine-similarity search on the 5th-generation tensor cores.
+//
+// Replaces B calls of cslam/nns_matching.py:61-63 (one per query; the reference API is
+// single-query) by ONE pass over the database: S[rows x B] = X[rows x dim] * Q[B x dim]^T on
+// tcgen05.mma kind::tf32 with fp32 accumulators in TMEM, 3xTF32 split precision
+//     x*q ~= x_lo*q_hi + x_hi*q_lo + x_hi*q_hi,   x_hi = tf32(x), x_lo = tf32(x - x_hi)
+// so similarities agree with the reference's fp32 arithmetic to ~1e-6 relative, and a fused
+// per-query top-k epilogue, so the rows x B similarity matrix never exists in memory.
+//
+// The tensor core accumulates in fp32 with truncation, a bias that grows with the number of
+// accumulations (dim/8 * 3) and with the magnitude of the running sum.  To keep the running sum small
+// the QUERY IS CENTRED:  x.q = x.(q - c) + c * sum(x),  c = mean(q).  The converter warps accumulate
+// sum(x) next to |x|^2 (they touch every element anyway) and the epilogue adds c * sum(x) back in
+// fp32, so the identity is exact and the accumulated part is ~10x smaller for non-negative data.
+//
+// Tensor-bound: algorithmic flops per launch = 2 * n * dim * B (issued: 3x that).
+// Algorithmic HBM bytes per launch = n * ld * 4 (the DB is read exactly once per batch of <= 256).
+//
+// One persistent CTA per SM, tiles of 128 database rows, K blocks of 32 floats (one 128-byte
+// swizzle row).  Warp roles (320 threads):
+//   warps 0-3  epilogue   tcgen05.ld the accumulator (lane == database row), scale by the row's and
+//                         the query's inverse norms, compare against the per-query threshold and
+//                         queue the rare survivors; per-query sorted lists live in shared memory
+//   warps 4-7  converter  split each landed database tile: write x_hi back in place and x_lo to a
+//                         second tile at the same (swizzled) offsets, accumulate |x|^2 per row
+//   warp  8    producer   TMA (cp.async.bulk.tensor, 128B swizzle) of the raw database tile and of the
+//                         pre-split query tiles q_hi / q_lo into a multi-stage ring
+//   warp  9    MMA        one elected lane issues 3 x 4 tcgen05.mma per K block; tcgen05.commit frees
+//                         the ring slot / publishes the accumulator; owns the TMEM allocation
+// The accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps the
+// MMAs of tile i+1.
+#include <cuda.h>
+
 #include "common.cuh"
 #include "kernels.h"
+
 namespace cslam {
-bool k2_supported(int, int) { return false; }
-int k2_grid(long long, int num_sms) { return num_sms; }
-cudaError_t k2_prepare(const float*, int, int, int, float*, float*, cudaStream_t) { return cudaErrorNotSupported; }
-cudaError_t k2_launch(const K2Args&, int, cudaStream_t, const char** err) { if (err) *err = "k2 not built"; return cudaErrorNotSupported; }
+namespace {
+
+constexpr int BM = 128;          // database rows per tile (UMMA M)
+constexpr int BK = 32;           // floats per K block = 128 bytes = one swizzle row
+constexpr int kEpiThreads = 128, kConvThreads = 128;
+constexpr int kThreads = 320;
+constexpr int kQueueCap = 256;   // per epilogue warp and 8-query chunk: 2 queries x 128 rows
+constexpr int kTmemCols = 512;
+
+struct K2Dev {
+  long long n;
+  int dim;
+  int B;        // real queries
+  int BN;       // padded to a multiple of 16 (UMMA N)
+  int k;
+  int stages;
+  int kblocks;  // ceil(dim / 32)
+  uint32_t idesc;
+  const float* inv_qn;
+  const float* q_mean;
+  u64* part_keys;  // [grid][B][k]
+};
+
+// shared-memory carve-up (offsets from a 1024-byte aligned base)
+struct Smem {
+  uint32_t stage_bytes, a_lo_off, b_hi_off, b_lo_off;  // within a stage (a_raw at 0)
+  uint32_t lists_off, thr_off, invq_off, qmean_off, queue_off, qcnt_off, norm_off, bars_off, tmem_off, total;
+};
+
+__host__ __device__ inline Smem carve(int BN, int B, int k, int stages) {
+  Smem s;
+  s.a_lo_off = BM * BK * 4;
+  s.b_hi_off = 2 * BM * BK * 4;
+  s.b_lo_off = s.b_hi_off + (uint32_t)BN * BK * 4;
+  s.stage_bytes = s.b_lo_off + (uint32_t)BN * BK * 4;  // multiple of 1024 because BN % 16 == 0 -> BN*128 % 1024? see below
+  s.stage_bytes = (s.stage_bytes + 1023u) & ~1023u;
+  uint32_t o = s.stage_bytes * (uint32_t)stages;
+  s.lists_off = o;  o += (uint32_t)B * k * 8;
+  s.thr_off = o;    o += (uint32_t)BN * 4;
+  s.invq_off = o;   o += (uint32_t)BN * 4;
+  s.qmean_off = o;  o += (uint32_t)BN * 4;
+  o = (o + 7u) & ~7u;
+  s.queue_off = o;  o += 4u * kQueueCap * 8;
+  s.qcnt_off = o;   o += 16;
+  s.norm_off = o;   o += 4u * BM * 4;  // [2][BM] |x|^2 then [2][BM] sum(x)
+  o = (o + 7u) & ~7u;
+  s.bars_off = o;   o += (3u * 16 + 6) * 8;   // full/conv/empty (<=16 stages) + 3 x 2 accumulator barriers
+  s.tmem_off = o;   o += 16;
+  s.total = o;
+  return s;
 }
+
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+  // K-major operand, 128-byte swizzle: 8-row atoms of 1024 bytes (SBO), LBO unused (1), version 1
+  return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+
+__device__ __forceinline__ float tf32_hi(float x) {
+  return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+}
+__device__ __forceinline__ float tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_qhi,
+          const __grid_constant__ CUtensorMap map_qlo, const K2Dev p) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024 the swizzle needs
+  unsigned char* smem = reinterpret_cast<unsigned char*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const Smem L = carve(p.BN, p.B, p.k, p.stages);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int S = p.stages;
+
+  u64* lists = reinterpret_cast<u64*>(smem + L.lists_off);
+  uint32_t* thr32 = reinterpret_cast<uint32_t*>(smem + L.thr_off);
+  float* invq = reinterpret_cast<float*>(smem + L.invq_off);
+  float* qmean = reinterpret_cast<float*>(smem + L.qmean_off);
+  u64* queue = reinterpret_cast<u64*>(smem + L.queue_off);
+  int* qcnt = reinterpret_cast<int*>(smem + L.qcnt_off);
+  float* norms = reinterpret_cast<float*>(smem + L.norm_off);
+  float* sums = norms + 2 * BM;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars_off);
+  uint64_t* full_bar = bars;             // [S]  TMA landed
+  uint64_t* conv_bar = bars + 16;        // [S]  x_hi / x_lo written
+  uint64_t* empty_bar = bars + 32;       // [S]  MMAs that read the stage are done
+  uint64_t* acc_full = bars + 48;        // [2]  accumulator complete
+  uint64_t* acc_empty = bars + 50;       // [2]  accumulator drained by the epilogue
+  uint64_t* norm_bar = bars + 52;        // [2]  row norms of the tile are in smem
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
+
+  // ---- one-time setup -----------------------------------------------------------------------------
+  for (int i = tid; i < p.B * p.k; i += kThreads) lists[i] = 0ull;
+  for (int i = tid; i < p.BN; i += kThreads) {
+    thr32[i] = 0u;
+    invq[i] = i < p.B ? p.inv_qn[i] : 0.f;
+    qmean[i] = i < p.B ? p.q_mean[i] : 0.f;
+  }
+  if (tid < 4) qcnt[tid] = 0;
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&conv_bar[s], kConvThreads);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], kEpiThreads);
+      mbar_init(&norm_bar[a], kConvThreads);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 9) tmem_alloc<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long tiles = (p.n + BM - 1) / BM;
+  const long long my_tiles =
+      (long long)blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+  if (warp == 8) {
+    // ===== TMA producer =============================================================================
+    if (lane == 0) {
+      tma_prefetch_desc(&map_a);
+      tma_prefetch_desc(&map_qhi);
+      tma_prefetch_desc(&map_qlo);
+      const uint32_t tx = (uint32_t)(BM * BK * 4 + 2 * p.BN * BK * 4);
+      long long it = 0;
+      for (long long t = 0; t < my_tiles; ++t) {
+        const int row0 = (int)((blockIdx.x + t * gridDim.x) * BM);
+        for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+          const int s = (int)(it % S);
+          mbar_wait(&empty_bar[s], (uint32_t)(((it / S) & 1) ^ 1));
+          unsigned char* st = smem + (size_t)s * L.stage_bytes;
+          mbar_expect_tx(&full_bar[s], tx);
+          tma_load_2d(st, &map_a, kb * BK, row0, &full_bar[s]);
+          tma_load_2d(st + L.b_hi_off, &map_qhi, kb * BK, 0, &full_bar[s]);
+          tma_load_2d(st + L.b_lo_off, &map_qlo, kb * BK, 0, &full_bar[s]);
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ===== MMA issuer ===============================================================================
+    if (lane == 0) {
+      long long it = 0;
+      for (long long t = 0; t < my_tiles; ++t) {
+        const int a = (int)(t & 1);
+        mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(a * p.BN);
+        for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+          const int s = (int)(it % S);
+          const uint32_t ph = (uint32_t)((it / S) & 1);
+          mbar_wait(&full_bar[s], ph);
+          mbar_wait(&conv_bar[s], ph);
+          tc_fence_after();
+          const uint32_t st = smem_u32(smem + (size_t)s * L.stage_bytes);
+#pragma unroll
+          for (int ks = 0; ks < BK / 8; ++ks) {
+            const uint64_t a_hi = make_desc(st + ks * 32);
+            const uint64_t a_lo = make_desc(st + L.a_lo_off + ks * 32);
+            const uint64_t b_hi = make_desc(st + L.b_hi_off + ks * 32);
+            const uint64_t b_lo = make_desc(st + L.b_lo_off + ks * 32);
+            umma_tf32_ss(d_tmem, a_lo, b_hi, p.idesc, (kb | ks) != 0 ? 1u : 0u);
+            umma_tf32_ss(d_tmem, a_hi, b_lo, p.idesc, 1u);
+            umma_tf32_ss(d_tmem, a_hi, b_hi, p.idesc, 1u);
+          }
+          umma_commit(&empty_bar[s]);  // implies tcgen05.fence::before_thread_sync
+        }
+        umma_commit(&acc_full[a]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== converter: x -> (x_hi in place, x_lo), row norms ==========================================
+    const int r = tid - 4 * 32;  // tile row owned by this thread
+    long long it = 0;
+    for (long long t = 0; t < my_tiles; ++t) {
+      const int a = (int)(t & 1);
+      float nn = 0.f, sx = 0.f;
+      for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+        const int s = (int)(it % S);
+        mbar_wait(&full_bar[s], (uint32_t)((it / S) & 1));
+        unsigned char* st = smem + (size_t)s * L.stage_bytes;
+        float4* raw = reinterpret_cast<float4*>(st + (size_t)r * 128);
+        float4* lo = reinterpret_cast<float4*>(st + L.a_lo_off + (size_t)r * 128);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int c = (i + r) & 7;  // rotate the 16-byte chunk order: conflict-free across the warp
+          const float4 x = raw[c];
+          float4 h, l;
+          h.x = tf32_hi(x.x); h.y = tf32_hi(x.y); h.z = tf32_hi(x.z); h.w = tf32_hi(x.w);
+          l.x = tf32_rna(x.x - h.x); l.y = tf32_rna(x.y - h.y);
+          l.z = tf32_rna(x.z - h.z); l.w = tf32_rna(x.w - h.w);
+          nn = fmaf(x.x, x.x, nn); nn = fmaf(x.y, x.y, nn);
+          nn = fmaf(x.z, x.z, nn); nn = fmaf(x.w, x.w, nn);
+          sx += (x.x + x.y) + (x.z + x.w);
+          raw[c] = h;
+          lo[c] = l;
+        }
+        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+        mbar_arrive(&conv_bar[s]);
+      }
+      // the epilogue of tile t-2 must be done with norms[a] before it is overwritten
+      mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
+      norms[a * BM + r] = nn;
+      sums[a * BM + r] = sx;
+      mbar_arrive(&norm_bar[a]);
+    }
+  } else {
+    // ===== epilogue: TMEM -> similarities -> per-query top-k ========================================
+    const int r = tid;  // accumulator lane == tile row; warp w may only touch lanes 32w .. 32w+31
+    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+    u64* myq = queue + (size_t)warp * kQueueCap;  // the queue this warp DRAINS (queries q & 3 == warp)
+    for (long long t = 0; t < my_tiles; ++t) {
+      const int a = (int)(t & 1);
+      const uint32_t ph = (uint32_t)((t >> 1) & 1);
+      const long long row0 = (blockIdx.x + t * gridDim.x) * (long long)BM;
+      mbar_wait(&norm_bar[a], ph);
+      mbar_wait(&acc_full[a], ph);
+      tc_fence_after();
+      const bool row_ok = row0 + r < p.n;
+      // 1 / max(|x|, eps)  ==  rsqrt(max(|x|^2, eps^2))
+      const float inv_nx = rsqrtf(fmaxf(norms[a * BM + r], kEps * kEps));
+      const float sum_x = sums[a * BM + r];
+      for (int c0 = 0; c0 < p.BN; c0 += 8) {
+        uint32_t v[8];
+        tmem_ld_32x32b_x8(tmem_base + lane_base + (uint32_t)(a * p.BN + c0), v);
+        tmem_ld_wait();
+        if (c0 < p.B) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int q = c0 + j;
+            const float s_ = fmaf(qmean[q], sum_x, __uint_as_float(v[j])) * inv_nx * invq[q];
+            const uint32_t o = sim_to_ord(s_);
+            if (row_ok && q < p.B && o > thr32[q]) {
+              const int slot = atomicAdd(&qcnt[q & 3], 1);
+              queue[(size_t)(q & 3) * kQueueCap + slot] = ((u64)o << 32) | ((u64)q << 8) | (u64)r;
+            }
+          }
+          named_bar_sync(1, kEpiThreads);
+          // drain: this warp owns the queries with q & 3 == warp, so no two warps touch one list
+          const int cnt = qcnt[warp];
+          for (int e = 0; e < cnt; ++e) {
+            const u64 ent = myq[e];
+            const int q = (int)((ent >> 8) & 0xff);
+            const uint32_t row = (uint32_t)(row0 + (long long)(ent & 0x7f));
+            const u64 key = (ent & 0xffffffff00000000ull) | (u64)(~row);
+            u64* lst = lists + (size_t)q * p.k;
+            u64 mine = lane < p.k ? lst[lane] : 0ull;
+            const u64 last = __shfl_sync(kFull, mine, p.k - 1);
+            if (key > last) {
+              const int pos = __popc(__ballot_sync(kFull, lane < p.k && mine > key));
+              const u64 up = __shfl_up_sync(kFull, mine, 1);
+              if (lane < p.k) {
+                if (lane > pos) mine = up;
+                else if (lane == pos) mine = key;
+                lst[lane] = mine;
+              }
+              const u64 nl = __shfl_sync(kFull, mine, p.k - 1);
+              if (lane == 0 && nl != 0ull) thr32[q] = (uint32_t)(nl >> 32);
+            }
+            __syncwarp();
+          }
+          __syncwarp();
+          if (lane == 0) qcnt[warp] = 0;
+          named_bar_sync(1, kEpiThreads);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[a]);
+    }
+    // this CTA's lists -> global scratch (all CTAs write, also the ones without tiles)
+    named_bar_sync(1, kEpiThreads);
+    u64* out = p.part_keys + (size_t)blockIdx.x * p.B * p.k;
+    for (int i = tid; i < p.B * p.k; i += kEpiThreads) out[i] = lists[i];
+  }
+
+  // ---- teardown -----------------------------------------------------------------------------------
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}
+
+// q -> c = mean(q), (q - c) split into q_hi (tf32-exact) and q_lo (tf32 residual), 1 / max(|q|, eps);
+// one block per query
+__global__ void k2_prepare_kernel(const float* __restrict__ q, int dim, int q_ld, float* q_hi,
+                                  float* q_lo, float* inv_qn, float* q_mean) {
+  const int b = blockIdx.x;
+  const float* src = q + (size_t)b * q_ld;
+  __shared__ float red[2][32];
+  __shared__ float mean_s;
+  float part = 0.f, sum = 0.f;
+  for (int i = threadIdx.x; i < dim; i += blockDim.x) {
+    const float x = src[i];
+    part = fmaf(x, x, part);
+    sum += x;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    part += __shfl_xor_sync(kFull, part, off);
+    sum += __shfl_xor_sync(kFull, sum, off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = part;
+    red[1][threadIdx.x >> 5] = sum;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f, u = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+      t += red[0][w];
+      u += red[1][w];
+    }
+    inv_qn[b] = 1.0f / fmaxf(sqrtf(t), kEps);
+    const float c = u / (float)dim;
+    mean_s = (c == c && fabsf(c) < 3.0e38f) ? c : 0.f;  // NaN/Inf queries: no centring
+    q_mean[b] = mean_s;
+  }
+  __syncthreads();
+  const float c = mean_s;
+  for (int i = threadIdx.x; i < q_ld; i += blockDim.x) {
+    const float x = i < dim ? src[i] - c : 0.f;
+    const float h = tf32_hi(x);
+    q_hi[(size_t)b * q_ld + i] = h;
+    q_lo[(size_t)b * q_ld + i] = tf32_rna(x - h);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+bool encode_map(void* fn, CUtensorMap* m, const float* base, long long rows, int dim, int ld,
+                int box_rows, CUtensorMapL2promotion promo) {
+  const cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)ld * 4};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return reinterpret_cast<EncodeTiledFn>(fn)(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                                             const_cast<float*>(base), gdim, gstr, box, estr,
+                                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                             promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+constexpr size_t kSmemCap = 227 * 1024;
+
+int pad_batch(int B) { return (B + 15) / 16 * 16; }
+
+int pick_stages(int B, int k) {
+  const int BN = pad_batch(B);
+  for (int s = 8; s >= 2; --s)
+    if ((size_t)carve(BN, B, k, s).total + 1024 <= kSmemCap) return s;
+  return 0;
+}
+
+}  // namespace
+
+bool k2_supported(int B, int k) {
+  return B >= 1 && B <= kK2MaxBatch && k >= 1 && k <= 32 && pick_stages(B, k) >= 2;
+}
+
+int k2_grid(long long n, int num_sms) {
+  const long long tiles = (n + BM - 1) / BM;
+  return (int)(tiles < num_sms ? (tiles < 1 ? 1 : tiles) : num_sms);
+}
+
+// q_lo buffer layout: [q_hi plane (B x q_ld)][q_lo plane (B x q_ld)] — callers size it 2x
+cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_planes, float* inv_qn,
+                       cudaStream_t stream) {
+  // inv_qn buffer layout: [inv_qn (B)][q_mean (B)] — callers size it 2x
+  k2_prepare_kernel<<<B, 128, 0, stream>>>(q, dim, q_ld, q_planes, q_planes + (size_t)B * q_ld, inv_qn,
+                                          inv_qn + B);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
+  K2Dev p;
+  p.n = a.n;
+  p.dim = a.dim;
+  p.B = a.B;
+  p.BN = pad_batch(a.B);
+  p.k = a.k;
+  p.stages = pick_stages(a.B, a.k);
+  p.kblocks = (a.dim + BK - 1) / BK;
+  p.inv_qn = a.inv_qn;
+  p.q_mean = a.inv_qn + a.B;
+  p.part_keys = a.part_keys;
+  // kind::tf32, fp32 accumulate, both operands K-major: c_format=F32(1)<<4, a/b_format=TF32(2)<<7/<<10,
+  // N>>3 at bit 17, M>>4 at bit 24
+  p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  if (p.stages < 2) {
+    if (err) *err = "k2: batch * k does not fit shared memory";
+    return cudaErrorInvalidConfiguration;
+  }
+  CUtensorMap ma, mh, ml;
+  const float* q_hi = a.q_lo;  // planes written by k2_prepare
+  const float* q_lo = a.q_lo + (size_t)a.B * a.q_ld;
+  if (!encode_map(a.encode_fn, &ma, a.db, a.n, a.dim, a.ld, BM, CU_TENSOR_MAP_L2_PROMOTION_L2_128B) ||
+      !encode_map(a.encode_fn, &mh, q_hi, a.B, a.dim, a.q_ld, p.BN, CU_TENSOR_MAP_L2_PROMOTION_L2_256B) ||
+      !encode_map(a.encode_fn, &ml, q_lo, a.B, a.dim, a.q_ld, p.BN, CU_TENSOR_MAP_L2_PROMOTION_L2_256B)) {
+    if (err) *err = "k2: cuTensorMapEncodeTiled failed";
+    return cudaErrorInvalidValue;
+  }
+  const size_t smem = carve(p.BN, p.B, p.k, p.stages).total + 1024;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(k2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  const int grid = k2_grid(a.n, num_sms);
+  k2_kernel<<<grid, kThreads, smem, stream>>>(ma, mh, ml, p);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace cslam
