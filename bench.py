@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (debugging only)")
+    ap.add_argument("--dim", type=int, default=0, help="override the descriptor size (debugging only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -181,6 +182,8 @@ def main():
     rows, dim, batch, k, _ = WORKLOADS[args.workload]
     if args.rows:
         rows = args.rows
+    if args.dim:
+        dim = args.dim
     if args.impl == "reference":
         return reference_arm(args, rows, dim, batch, k)
 

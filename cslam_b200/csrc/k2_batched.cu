@@ -403,11 +403,11 @@ int pick_stages(int B, int k) {
 
 }  // namespace
 
-bool k2_supported(int B, int k) {
+bool k2s_supported(int B, int k) {
   return B >= 1 && B <= kK2MaxBatch && k >= 1 && k <= 32 && pick_stages(B, k) >= 2;
 }
 
-int k2_grid(long long n, int num_sms) {
+int k2s_grid(long long n, int num_sms) {
   const long long tiles = (n + BM - 1) / BM;
   return (int)(tiles < num_sms ? (tiles < 1 ? 1 : tiles) : num_sms);
 }
@@ -422,7 +422,7 @@ cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_planes
   return cudaGetLastError();
 }
 
-cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
+cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
   K2Dev p;
   p.n = a.n;
   p.dim = a.dim;
@@ -459,7 +459,7 @@ cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const c
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  const int grid = k2_grid(a.n, num_sms);
+  const int grid = k2s_grid(a.n, num_sms);
   k2_kernel<<<grid, kThreads, smem, stream>>>(ma, mh, ml, p);
   count_launch();
   return cudaGetLastError();

@@ -74,6 +74,10 @@ int k2_grid(long long n, int num_sms);
 cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_lo, float* inv_qn,
                        cudaStream_t stream);
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err);
+// one-CTA-per-tile predecessor (k2_batched.cu), kept selectable with CSLAM_NNS_K2_LEGACY=1 for A/B timing
+bool k2s_supported(int B, int k);
+int k2s_grid(long long n, int num_sms);
+cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err);
 
 // launch counter shared by all kernels (reported through cslam_nns_launch_count)
 void count_launch(int n = 1);
