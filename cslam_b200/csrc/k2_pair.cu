@@ -521,7 +521,7 @@ cudaError_t plaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  const int grid = k2_grid(a.n, num_sms);
+  const int grid = k2p_grid(a.n, num_sms);
   static u64* prof_buf = nullptr;
   static const bool want_prof = getenv("CSLAM_NNS_K2_PROF") != nullptr;
   p.prof = nullptr;
@@ -553,22 +553,19 @@ cudaError_t plaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
 
 }  // namespace
 
-bool k2_supported(int B, int k) {
-  if (env_legacy()) return k2s_supported(B, k);
+bool k2p_supported(int B, int k) {
   return B >= 1 && B <= kK2MaxBatch && k >= 1 && k <= 32 &&
          (env_bk() == 32 ? ppick_stages<32>(B, k) : ppick_stages<16>(B, k)) >= 2;
 }
 
 // CTAs launched (= partial lists written): one CTA pair per 256-row super tile, at most one pair per 2 SMs
-int k2_grid(long long n, int num_sms) {
-  if (env_legacy()) return k2s_grid(n, num_sms);
+int k2p_grid(long long n, int num_sms) {
   const long long tiles2 = (n + 2 * BM - 1) / (2 * BM);
   const long long pairs = num_sms / 2;
   return (int)(2 * (tiles2 < pairs ? (tiles2 < 1 ? 1 : tiles2) : pairs));
 }
 
-cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
-  if (env_legacy()) return k2s_launch(a, num_sms, stream, err);
+cudaError_t k2p_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
   return env_bk() == 32 ? plaunch<32>(a, num_sms, stream, err) : plaunch<16>(a, num_sms, stream, err);
 }
 

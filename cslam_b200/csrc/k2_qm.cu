@@ -1,0 +1,596 @@
+// K2 (query-major pair variant) — batched cosine-similarity search, 129..256 queries per pass.
+//
+// Replaces B calls of cslam/nns_matching.py:61-63 by ONE pass over the database.  Two CTAs of a cluster
+// form one tcgen05 cta_group::2 pair and compute, per 256-row super tile of the database,
+//     S[256 queries x 256 rows] = Q[256 x dim] * X[256 x dim]^T            (3xTF32, fp32 accumulate in TMEM)
+// with the QUERIES on the MMA's M side: CTA r owns queries 128r .. 128r+127 (A operand, its TMEM lanes)
+// and stages database rows 128r .. 128r+127 of the super tile (its half of the B operand).  Compared with
+// the row-major pair kernel (k2_pair.cu) the shared-memory contents per CTA are identical — 128 database
+// rows (raw -> x_hi, x_lo) and 128 queries (q_hi, q_lo) per K block — but the accumulator comes out with
+// TMEM lane == query, so every epilogue thread owns ONE query and keeps its top-k list privately:
+// no warp collectives, no locks, a register threshold, and a warm-up that costs k*ln(256/k) scalar
+// insertions per thread instead of k warp-wide extractions per (warp, query).
+//
+//   warp  roles (384 threads per CTA; both CTAs run every role except the MMA issue)
+//   0-3   epilogue   thread t <-> query 128*rank + t: tcgen05.ld 32 columns (= database rows) at a time,
+//                    s = (acc + mean(q) * sum(x)) * inv|x| * inv|q|, compare with the thread's threshold,
+//                    insert into the thread's sorted list (shared memory, [k][128] so lanes never conflict)
+//   4     X producer  TMA of this CTA's 128 database rows (L2 evict-first)
+//   5     MMA         leader CTA only: 3 products x (BK/8) tcgen05.mma.cta_group::2 per K block;
+//                     tcgen05.commit multicast frees the ring slot / publishes the accumulator in both CTAs
+//   6     Q producer  ONE 3-D TMA for this CTA's 128 rows of q_hi and q_lo (L2 evict-last); the bytes are
+//                     counted on the LEADER's barrier (cp.async.bulk.tensor .cta_group::2)
+//   8-11  converter   split the landed rows (x_hi in place, x_lo beside it), accumulate |x|^2 and sum(x);
+//                     at the end of a tile write 1/max(|x|,eps) and sum(x) into BOTH CTAs' norm arrays
+//                     (st.shared::cluster) because both epilogues need all 256 rows of the super tile
+//
+// Tensor-bound: algorithmic flops per launch = 2 * n * dim * 256-padded batch (issued: 3x).
+// Algorithmic HBM bytes per launch = n * ld * 4 (the database is read exactly once per pass).
+#include <cuda.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace cslam {
+namespace {
+
+constexpr int BM = 128;   // queries per CTA (MMA M = 256 over the pair) and database rows per CTA and tile
+constexpr int BN2 = 256;  // database rows per super tile (MMA N)
+constexpr int kThreads = 384;
+constexpr int kTmemCols = 512;
+constexpr int kMaxStages = 12;
+
+struct QDev {
+  long long n;
+  long long tiles2;  // 256-row super tiles
+  int dim, B, k, stages, kblocks, dbg;
+  uint32_t idesc;
+  const float* inv_qn;
+  const float* q_mean;
+  u64* part_keys;  // [pairs][B][k]
+  u64* prof;
+};
+
+struct QSmem {
+  uint32_t tile_bytes, x_lo_off, q_hi_off, q_lo_off, stage_bytes;
+  uint32_t lists_off, norm_off, bars_off, tmem_off, total;
+};
+
+template <int BK>
+__host__ __device__ inline QSmem qcarve(int k, int stages) {
+  QSmem s;
+  s.tile_bytes = BM * BK * 4;
+  s.x_lo_off = s.tile_bytes;
+  s.q_hi_off = 2 * s.tile_bytes;
+  s.q_lo_off = 3 * s.tile_bytes;
+  s.stage_bytes = 4 * s.tile_bytes;  // 16 KB (BK = 32) or 8 KB (BK = 16) per tile: multiple of 1024
+  uint32_t o = s.stage_bytes * (uint32_t)stages;
+  s.lists_off = o;  o += (uint32_t)BM * k * 8;         // [k][128] keys
+  s.norm_off = o;   o += 2u * 2u * BN2 * 4;            // [2 accumulators][inv|x| (256), sum(x) (256)]
+  s.bars_off = o;   o += (4u * kMaxStages + 10u) * 8;
+  s.tmem_off = o;   o += 16;
+  s.total = o;
+  return s;
+}
+
+template <int BK>
+__device__ __forceinline__ uint64_t qdesc(uint32_t saddr) {
+  // K-major operand; rows of BK*4 bytes swizzled in 8-row atoms (SBO = 8 rows); LBO unused (1); version 1
+  constexpr uint64_t kLayout = BK == 32 ? 2 : 4;  // SWIZZLE_128B : SWIZZLE_64B
+  constexpr uint64_t kSbo = (8 * BK * 4) >> 4;
+  return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)1 << 16) | (kSbo << 32) | ((uint64_t)1 << 46) |
+         (kLayout << 61);
+}
+
+__device__ __forceinline__ float q_tf32_hi(float x) {
+  return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+}
+__device__ __forceinline__ float q_tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+// store to the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void st_cluster_f32(float* p, uint32_t cta, float v) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.f32 [ra], %2;\n\t}" ::"r"(smem_u32(p)),
+      "r"(cta), "f"(v)
+      : "memory");
+}
+__device__ __forceinline__ void fence_acq_rel_cluster() {
+  asm volatile("fence.acq_rel.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
+        "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]),
+        "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]),
+        "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+#define QPROF_WAIT(acc, stmt)                   \
+  do {                                          \
+    if (p.prof) {                               \
+      const long long t0__ = clock64();         \
+      stmt;                                     \
+      acc += clock64() - t0__;                  \
+    } else {                                    \
+      stmt;                                     \
+    }                                           \
+  } while (0)
+
+// Thread-private insertion into a descending list stored with stride 128 (entry j of this thread at lst[j * 128]).
+// Returns the new threshold (similarity of the k-th entry once the list is full).
+__device__ __noinline__ float private_insert(u64* lst, int k, u64 key, float thr) {
+  if (key <= lst[(k - 1) * BM]) return thr;
+  int j = k - 1;
+  while (j > 0) {
+    const u64 up = lst[(j - 1) * BM];
+    if (up >= key) break;
+    lst[j * BM] = up;
+    --j;
+  }
+  lst[j * BM] = key;
+  const u64 kth = lst[(k - 1) * BM];
+  return kth != 0ull ? key_sim(kth) : thr;
+}
+
+template <int BK>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
+           const QDev p) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  // identical layout in both CTAs (the pair MMA addresses the peer's operands by the leader's offsets)
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const QSmem L = qcarve<BK>(p.k, p.stages);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int S = p.stages;
+  const uint32_t rank = cluster_ctarank();
+  const long long pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+  u64* lists = reinterpret_cast<u64*>(smem + L.lists_off);
+  float* norms = reinterpret_cast<float*>(smem + L.norm_off);  // [a][0..255] inv|x|, [a][256..511] sum(x)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars_off);
+  uint64_t* full_bar = bars;                     // [S] local: own database rows landed
+  uint64_t* conv_bar = bars + kMaxStages;        // [S] LEADER: both CTAs' rows are split (8 warp arrivals)
+  uint64_t* empty_bar = bars + 2 * kMaxStages;   // [S] local: the pair MMAs that read the slot are done
+  uint64_t* qfull_bar = bars + 3 * kMaxStages;   // [S] LEADER: both CTAs' query tiles landed (tx bytes)
+  uint64_t* acc_full = bars + 4 * kMaxStages;    // [2] local: accumulator complete (multicast commit)
+  uint64_t* acc_empty = acc_full + 2;            // [2] both CTAs: all 8 epilogue warps are done with
+                                                 //     accumulator a and norms[a] (each warp arrives on both)
+  uint64_t* norm_bar = acc_full + 4;             // [2] local: all 256 rows' norms are in (8 converter warps)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
+
+  for (int i = tid; i < BM * p.k; i += kThreads) lists[i] = 0ull;
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&conv_bar[s], 8);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&qfull_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], 8);
+      mbar_init(&norm_bar[a], 8);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 5) tmem_alloc_pair<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long my_tiles = pair < p.tiles2 ? (p.tiles2 - pair + npairs - 1) / npairs : 0;
+
+  if (warp == 4) {
+    // ===== X producer ===============================================================================
+    if (lane == 0) {
+      tma_prefetch_desc(&map_x);
+      long long w0 = 0;
+      const long long tstart = clock64();
+      int s = 0;
+      uint32_t ph = 0;  // ring position and wrap parity, advanced incrementally (no div/mod per stage)
+      for (long long t = 0; t < my_tiles; ++t) {
+        const int row0 = (int)(((pair + t * npairs) * 2 + rank) * BM);
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
+          QPROF_WAIT(w0, mbar_wait(&empty_bar[s], ph ^ 1));
+          mbar_expect_tx(&full_bar[s], L.tile_bytes);
+          tma_load_2d_hint(smem + (size_t)s * L.stage_bytes, &map_x, kb * BK, row0, &full_bar[s], kEvictFirst);
+        }
+      }
+      if (p.prof) {
+        p.prof[blockIdx.x * 16 + 0] = (u64)w0;
+        p.prof[blockIdx.x * 16 + 7] = (u64)(clock64() - tstart);
+      }
+    }
+  } else if (warp == 6) {
+    // ===== Q producer ===============================================================================
+    if (lane == 0) {
+      tma_prefetch_desc(&map_q);
+      long long w0 = 0;
+      int s = 0;
+      uint32_t ph = 0;
+      for (long long t = 0; t < my_tiles; ++t) {
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
+          QPROF_WAIT(w0, mbar_wait(&empty_bar[s], ph ^ 1));
+          if (rank == 0) mbar_expect_tx(&qfull_bar[s], 4u * L.tile_bytes);
+          tma_load_3d_pair(smem + (size_t)s * L.stage_bytes + L.q_hi_off, &map_q, kb * BK, (int)rank * BM, 0,
+                           &qfull_bar[s], kEvictLast);
+        }
+      }
+      if (p.prof) p.prof[blockIdx.x * 16 + 1] = (u64)w0;
+    }
+  } else if (warp == 5) {
+    // ===== MMA issuer (leader CTA only) =============================================================
+    if (rank == 0 && lane == 0) {
+      long long w0 = 0, w1 = 0, w2 = 0;
+      int s = 0;
+      uint32_t ph = 0;
+      for (long long t = 0; t < my_tiles; ++t) {
+        const int a = (int)(t & 1);
+        QPROF_WAIT(w2, mbar_wait_cluster(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN2);
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
+          QPROF_WAIT(w0, mbar_wait_cluster(&qfull_bar[s], ph));
+          QPROF_WAIT(w1, mbar_wait_cluster(&conv_bar[s], ph));
+          tc_fence_after();
+          const uint32_t st = smem_u32(smem + (size_t)s * L.stage_bytes);
+#pragma unroll
+          for (int ks = 0; ks < BK / 8; ++ks) {
+            const uint64_t x_hi = qdesc<BK>(st + ks * 32);
+            const uint64_t x_lo = qdesc<BK>(st + L.x_lo_off + ks * 32);
+            const uint64_t q_hi = qdesc<BK>(st + L.q_hi_off + ks * 32);
+            const uint64_t q_lo = qdesc<BK>(st + L.q_lo_off + ks * 32);
+            if (!(p.dbg & 2)) {
+              umma_tf32_ss_pair(d_tmem, q_hi, x_lo, p.idesc, (kb | ks) != 0 ? 1u : 0u);
+              umma_tf32_ss_pair(d_tmem, q_lo, x_hi, p.idesc, 1u);
+              umma_tf32_ss_pair(d_tmem, q_hi, x_hi, p.idesc, 1u);
+            } else {
+              umma_tf32_ss_pair(d_tmem, q_hi, x_hi, p.idesc, (kb | ks) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit_pair(&empty_bar[s]);
+        }
+        umma_commit_pair(&acc_full[a]);
+      }
+      if (p.prof) {
+        p.prof[blockIdx.x * 16 + 2] = (u64)w0;
+        p.prof[blockIdx.x * 16 + 3] = (u64)w1;
+        p.prof[blockIdx.x * 16 + 4] = (u64)w2;
+      }
+    }
+  } else if (warp >= 8) {
+    // ===== converter ===============================================================================
+    const int r = tid - 8 * 32;  // row of this CTA's 128-row tile
+    constexpr int kChunks = BK / 4;  // 16-byte chunks per row
+    int s = 0;
+    uint32_t ph = 0;
+    long long w0 = 0, wce = 0, wcf = 0;
+    for (long long t = 0; t < my_tiles; ++t) {
+      const int a = (int)(t & 1);
+      float nn = 0.f, sx = 0.f;
+      for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
+        QPROF_WAIT(w0, mbar_wait(&full_bar[s], ph));
+        unsigned char* st = smem + (size_t)s * L.stage_bytes;
+        if (!(p.dbg & 1)) {
+          float4* raw = reinterpret_cast<float4*>(st + (size_t)r * (BK * 4));
+          float4* lo = reinterpret_cast<float4*>(st + L.x_lo_off + (size_t)r * (BK * 4));
+          float4 x[kChunks];
+#pragma unroll
+          for (int i = 0; i < kChunks; ++i) {
+            // rotate the chunk order so that a quarter-warp touches 8 distinct 16-byte bank groups
+            const int c = BK == 32 ? ((i + r) & 7) : ((i + (r >> 1)) & 3);
+            x[i] = raw[c];
+          }
+#pragma unroll
+          for (int i = 0; i < kChunks; ++i) {
+            const int c = BK == 32 ? ((i + r) & 7) : ((i + (r >> 1)) & 3);
+            float4 h, l;
+            h.x = q_tf32_hi(x[i].x); h.y = q_tf32_hi(x[i].y); h.z = q_tf32_hi(x[i].z); h.w = q_tf32_hi(x[i].w);
+            l.x = q_tf32_rna(x[i].x - h.x); l.y = q_tf32_rna(x[i].y - h.y);
+            l.z = q_tf32_rna(x[i].z - h.z); l.w = q_tf32_rna(x[i].w - h.w);
+            nn = fmaf(x[i].x, x[i].x, nn); nn = fmaf(x[i].y, x[i].y, nn);
+            nn = fmaf(x[i].z, x[i].z, nn); nn = fmaf(x[i].w, x[i].w, nn);
+            sx += (x[i].x + x[i].y) + (x[i].z + x[i].w);
+            raw[c] = h;
+            lo[c] = l;
+          }
+          fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(&conv_bar[s], 0);
+      }
+      // both epilogues must be done with norms[a] (tile t-2) before either converter overwrites it
+      QPROF_WAIT(wce, mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
+      float* ninv = norms + a * (2 * BN2) + rank * BM + r;
+      const float inv = rsqrtf(fmaxf(nn, kEps * kEps));  // 1 / max(|x|, eps)
+      ninv[0] = inv;
+      ninv[BN2] = sx;
+      st_cluster_f32(ninv, rank ^ 1u, inv);
+      st_cluster_f32(ninv + BN2, rank ^ 1u, sx);
+      QPROF_WAIT(wcf, fence_acq_rel_cluster());
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&norm_bar[a]);
+        mbar_arrive_cluster(&norm_bar[a], rank ^ 1u);
+      }
+    }
+    if (p.prof && tid == 8 * 32) {
+      p.prof[blockIdx.x * 16 + 5] = (u64)w0;
+      p.prof[blockIdx.x * 16 + 11] = (u64)wce;
+      p.prof[blockIdx.x * 16 + 12] = (u64)wcf;
+    }
+  } else if (warp < 4) {
+    // ===== epilogue: thread <-> query ===============================================================
+    const int q = (int)rank * BM + tid;
+    const bool valid = q < p.B;
+    const float qmean_r = valid ? p.q_mean[q] : 0.f;
+    const float invq_r = valid ? p.inv_qn[q] : 0.f;
+    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+    u64* lst = lists + tid;
+    float thr = -INFINITY;
+    long long wepi = 0, wnorm = 0, wfence = 0, wscan = 0;
+    for (long long t = 0; t < my_tiles; ++t) {
+      const int a = (int)(t & 1);
+      const uint32_t ph = (uint32_t)((t >> 1) & 1);
+      const long long row_base = (pair + t * npairs) * (long long)BN2;
+      const int valid_cols = (int)((p.n - row_base) < BN2 ? (p.n - row_base) : BN2);
+      QPROF_WAIT(wnorm, mbar_wait(&norm_bar[a], ph));
+      QPROF_WAIT(wfence, fence_acq_rel_cluster());  // the peer's half of norms[a] came through st.shared::cluster
+      QPROF_WAIT(wepi, mbar_wait(&acc_full[a], ph));
+      tc_fence_after();
+      const long long tscan0 = p.prof ? clock64() : 0;
+      const float* ninv = norms + a * (2 * BN2);
+      const float* nsum = ninv + BN2;
+      for (int c0 = 0; c0 < BN2; c0 += 32) {
+        if (c0 >= valid_cols || (p.dbg & 4)) break;
+        uint32_t v[32];
+        if (!(p.dbg & 32)) {
+          tmem_ld_32x32b_x32(tmem_base + lane_base + (uint32_t)(a * BN2 + c0), v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        // fast path: no branches, one survivor bit per column (the threshold is only read here; a stale
+        // value just sends a few extra candidates to the exact comparison below)
+        uint32_t m = 0u;
+#pragma unroll
+        for (int j4 = 0; j4 < 32; j4 += 4) {
+          const float4 iv = *reinterpret_cast<const float4*>(ninv + c0 + j4);
+          const float4 sm = *reinterpret_cast<const float4*>(nsum + c0 + j4);
+          const float iv_[4] = {iv.x, iv.y, iv.z, iv.w};
+          const float sm_[4] = {sm.x, sm.y, sm.z, sm.w};
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const float s_ = fmaf(qmean_r, sm_[jj], __uint_as_float(v[j4 + jj])) * iv_[jj] * invq_r;
+            v[j4 + jj] = __float_as_uint(s_);
+            // ties go to the exact key comparison (a lower row index wins); NaN passes and sorts first
+            m |= (!(s_ < thr) && c0 + j4 + jj < valid_cols) ? (1u << (j4 + jj)) : 0u;
+          }
+        }
+        if (!valid || (p.dbg & 16)) m = 0u;
+        const uint32_t um = __reduce_or_sync(kFull, m);
+        if (um != 0u) {  // rare after warm-up; the branches below are warp-uniform
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            if (um & (1u << j)) {
+              if (m & (1u << j))
+                thr = private_insert(lst, p.k,
+                                     ((u64)sim_to_ord(__uint_as_float(v[j])) << 32) |
+                                         (u64)(~(uint32_t)(row_base + c0 + j)),
+                                     thr);
+            }
+          }
+        }
+      }
+      if (p.prof) wscan += clock64() - tscan0;
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive_cluster(&acc_empty[a], 0);
+        mbar_arrive_cluster(&acc_empty[a], 1);
+      }
+    }
+    if (p.prof && tid == 0) {
+      p.prof[blockIdx.x * 16 + 6] = (u64)wepi;
+      p.prof[blockIdx.x * 16 + 8] = (u64)wnorm;
+      p.prof[blockIdx.x * 16 + 9] = (u64)wfence;
+      p.prof[blockIdx.x * 16 + 10] = (u64)wscan;
+    }
+    // this CTA's 128 queries -> part_keys[pair][q][k]
+    if (valid) {
+      u64* out = p.part_keys + ((size_t)pair * p.B + q) * p.k;
+      for (int j = 0; j < p.k; ++j) out[j] = lst[j * BM];
+    }
+  }
+
+  // ---- teardown -----------------------------------------------------------------------------------
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc_pair<kTmemCols>(tmem_base);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+bool qencode_x(void* fn, CUtensorMap* m, const float* base, long long rows, int dim, int ld, int bk) {
+  const cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)ld * 4};
+  const cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)BM};
+  const cuuint32_t estr[2] = {1, 1};
+  return reinterpret_cast<EncodeTiledFn>(fn)(
+             m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, bk == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+// the two planes written by k2_prepare (q_hi [B][q_ld] then q_lo [B][q_ld]) as ONE 3-D tensor
+bool qencode_q(void* fn, CUtensorMap* m, const float* planes, int B, int dim, int q_ld, int bk) {
+  const cuuint64_t gdim[3] = {(cuuint64_t)dim, (cuuint64_t)B, 2};
+  const cuuint64_t gstr[2] = {(cuuint64_t)q_ld * 4, (cuuint64_t)B * q_ld * 4};
+  const cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)BM, 2};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return reinterpret_cast<EncodeTiledFn>(fn)(
+             m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(planes), gdim, gstr, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, bk == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+constexpr size_t kSmemCap = 227 * 1024;
+
+template <int BK>
+int qpick_stages(int k) {
+  for (int s = kMaxStages; s >= 2; --s)
+    if ((size_t)qcarve<BK>(k, s).total + 1024 <= kSmemCap) return s;
+  return 0;
+}
+
+int q_env_bk() {
+  static int bk = 0;
+  if (!bk) {
+    const char* v = getenv("CSLAM_NNS_K2_BK");
+    bk = (v && atoi(v) == 16) ? 16 : 32;
+  }
+  return bk;
+}
+
+int q_pairs(long long n, int num_sms) {
+  const long long tiles2 = (n + BN2 - 1) / BN2;
+  const long long pairs = num_sms / 2;
+  return (int)(tiles2 < pairs ? (tiles2 < 1 ? 1 : tiles2) : pairs);
+}
+
+template <int BK>
+cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
+  QDev p;
+  p.n = a.n;
+  p.tiles2 = (a.n + BN2 - 1) / BN2;
+  p.dim = a.dim;
+  p.B = a.B;
+  p.k = a.k;
+  p.stages = qpick_stages<BK>(a.k);
+  {
+    const char* v = getenv("CSLAM_NNS_K2_STAGES");
+    if (v && atoi(v) >= 2 && atoi(v) < p.stages) p.stages = atoi(v);
+    v = getenv("CSLAM_NNS_K2_DBG");
+    p.dbg = v ? atoi(v) : 0;
+  }
+  p.kblocks = (a.dim + BK - 1) / BK;
+  p.inv_qn = a.inv_qn;
+  p.q_mean = a.inv_qn + a.B;
+  p.part_keys = a.part_keys;
+  // kind::tf32, fp32 accumulate, K-major operands; N>>3 at bit 17, M>>4 at bit 24 (M = 256 over the pair)
+  p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN2 >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+  if (p.stages < 2) {
+    if (err) *err = "k2: k does not fit shared memory";
+    return cudaErrorInvalidConfiguration;
+  }
+  CUtensorMap mx, mq;
+  if (!qencode_x(a.encode_fn, &mx, a.db, a.n, a.dim, a.ld, BK) ||
+      !qencode_q(a.encode_fn, &mq, a.q_lo, a.B, a.dim, a.q_ld, BK)) {
+    if (err) *err = "k2: cuTensorMapEncodeTiled failed";
+    return cudaErrorInvalidValue;
+  }
+  const size_t smem = qcarve<BK>(p.k, p.stages).total + 1024;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(k2q_kernel<BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  const int grid = 2 * q_pairs(a.n, num_sms);
+  static u64* prof_buf = nullptr;
+  static const bool want_prof = getenv("CSLAM_NNS_K2_PROF") != nullptr;
+  p.prof = nullptr;
+  if (want_prof) {
+    if (!prof_buf) cudaMalloc(&prof_buf, 1024 * 16 * sizeof(u64));
+    cudaMemsetAsync(prof_buf, 0, 1024 * 16 * sizeof(u64), stream);
+    p.prof = prof_buf;
+  }
+  k2q_kernel<BK><<<grid, kThreads, smem, stream>>>(mx, mq, p);
+  count_launch();
+  if (want_prof) {
+    static u64 hbuf[1024 * 16];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(hbuf, prof_buf, sizeof(hbuf), cudaMemcpyDeviceToHost);
+    const char* names[13] = {"Xprod wait empty", "Qprod wait empty", "MMA wait qfull", "MMA wait conv",
+                             "MMA wait acc_empty", "conv wait full", "epi wait acc_full", "total (Xprod)",
+                             "epi wait norm", "epi fence", "epi scan", "conv wait acc_empty", "conv fence"};
+    for (int r = 0; r < 2; ++r) {
+      fprintf(stderr, "[k2q prof] rank %d (avg cycles over %d CTAs, %d stages):", r, grid / 2, p.stages);
+      for (int i = 0; i < 13; ++i) {
+        double acc = 0;
+        for (int c = r; c < grid; c += 2) acc += (double)hbuf[c * 16 + i];
+        fprintf(stderr, "  %s=%.0f", names[i], acc / (grid / 2));
+      }
+      fprintf(stderr, "\n");
+    }
+  }
+  return cudaGetLastError();
+}
+
+// which kernel serves a batch of B: 0 = query-major pair kernel (this file), 1 = row-major pair kernel
+// (k2_pair.cu), 2 = one-CTA kernel (k2_batched.cu).  CSLAM_NNS_K2_FORCE=qm|pair|legacy overrides.
+int q_route(int B) {
+  static int forced = -2;
+  if (forced == -2) {
+    const char* v = getenv("CSLAM_NNS_K2_FORCE");
+    forced = !v ? -1 : !strcmp(v, "qm") ? 0 : !strcmp(v, "pair") ? 1 : !strcmp(v, "legacy") ? 2 : -1;
+  }
+  if (forced >= 0) return forced;
+  return B > 128 ? 0 : 1;
+}
+
+}  // namespace
+
+bool k2_supported(int B, int k) {
+  if (B < 1 || B > kK2MaxBatch || k < 1 || k > 32) return false;
+  switch (q_route(B)) {
+    case 0: return (q_env_bk() == 16 ? qpick_stages<16>(k) : qpick_stages<32>(k)) >= 2;
+    case 1: return k2p_supported(B, k);
+    default: return k2s_supported(B, k);
+  }
+}
+
+int k2_parts(long long n, int B, int num_sms) {
+  switch (q_route(B)) {
+    case 0: return q_pairs(n, num_sms);
+    case 1: return k2p_grid(n, num_sms);
+    default: return k2s_grid(n, num_sms);
+  }
+}
+
+cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
+  switch (q_route(a.B)) {
+    case 0: return q_env_bk() == 16 ? qlaunch<16>(a, num_sms, stream, err) : qlaunch<32>(a, num_sms, stream, err);
+    case 1: return k2p_launch(a, num_sms, stream, err);
+    default: return k2s_launch(a, num_sms, stream, err);
+  }
+}
+
+}  // namespace cslam
