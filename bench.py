@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the row count (debugging only)")
     ap.add_argument("--dim", type=int, default=0, help="override the descriptor size (debugging only)")
+    ap.add_argument("--batch", type=int, default=0, help="override the batch size (debugging only)")
+    ap.add_argument("--k", type=int, default=0, help="override k (debugging only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -184,6 +186,10 @@ def main():
         rows = args.rows
     if args.dim:
         dim = args.dim
+    if args.batch:
+        batch = args.batch
+    if args.k:
+        k = args.k
     if args.impl == "reference":
         return reference_arm(args, rows, dim, batch, k)
 

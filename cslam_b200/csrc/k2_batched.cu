@@ -168,12 +168,13 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       tma_prefetch_desc(&map_qhi);
       tma_prefetch_desc(&map_qlo);
       const uint32_t tx = (uint32_t)(BM * BK * 4 + 2 * p.BN * BK * 4);
-      long long it = 0;
+      int s = 0;
+      uint32_t ph = 0;  // ring position / wrap parity advanced incrementally: a 64-bit div/mod per stage in
+                        // a single-thread role costs ~500 clk of dependent latency
       for (long long t = 0; t < my_tiles; ++t) {
         const int row0 = (int)((blockIdx.x + t * gridDim.x) * BM);
-        for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
-          const int s = (int)(it % S);
-          mbar_wait(&empty_bar[s], (uint32_t)(((it / S) & 1) ^ 1));
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
           unsigned char* st = smem + (size_t)s * L.stage_bytes;
           mbar_expect_tx(&full_bar[s], tx);
           tma_load_2d(st, &map_a, kb * BK, row0, &full_bar[s]);
@@ -185,15 +186,14 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   } else if (warp == 9) {
     // ===== MMA issuer ===============================================================================
     if (lane == 0) {
-      long long it = 0;
+      int s = 0;
+      uint32_t ph = 0;
       for (long long t = 0; t < my_tiles; ++t) {
         const int a = (int)(t & 1);
         mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(a * p.BN);
-        for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
-          const int s = (int)(it % S);
-          const uint32_t ph = (uint32_t)((it / S) & 1);
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
           mbar_wait(&full_bar[s], ph);
           mbar_wait(&conv_bar[s], ph);
           tc_fence_after();
@@ -216,13 +216,13 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   } else if (warp >= 4) {
     // ===== converter: x -> (x_hi in place, x_lo), row norms ==========================================
     const int r = tid - 4 * 32;  // tile row owned by this thread
-    long long it = 0;
+    int s = 0;
+    uint32_t ph = 0;
     for (long long t = 0; t < my_tiles; ++t) {
       const int a = (int)(t & 1);
       float nn = 0.f, sx = 0.f;
-      for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
-        const int s = (int)(it % S);
-        mbar_wait(&full_bar[s], (uint32_t)((it / S) & 1));
+      for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
+        mbar_wait(&full_bar[s], ph);
         unsigned char* st = smem + (size_t)s * L.stage_bytes;
         float4* raw = reinterpret_cast<float4*>(st + (size_t)r * 128);
         float4* lo = reinterpret_cast<float4*>(st + L.a_lo_off + (size_t)r * 128);

@@ -1,13 +1,13 @@
-// K2 (query-major pair variant) — batched cosine-similarity search, 129..256 queries per pass.
+// K2 (query-major pair variant) — batched cosine-similarity search, 97..256 queries per pass (smaller batches: k2_batched.cu).
 //
 // Replaces B calls of cslam/nns_matching.py:61-63 by ONE pass over the database.  Two CTAs of a cluster
 // form one tcgen05 cta_group::2 pair and compute, per 256-row super tile of the database,
 //     S[256 queries x 256 rows] = Q[256 x dim] * X[256 x dim]^T            (3xTF32, fp32 accumulate in TMEM)
 // with the QUERIES on the MMA's M side: CTA r owns queries 128r .. 128r+127 (A operand, its TMEM lanes)
 // and stages database rows 128r .. 128r+127 of the super tile (its half of the B operand).  Compared with
-// the row-major pair kernel (k2_pair.cu) the shared-memory contents per CTA are identical — 128 database
-// rows (raw -> x_hi, x_lo) and 128 queries (q_hi, q_lo) per K block — but the accumulator comes out with
-// TMEM lane == query, so every epilogue thread owns ONE query and keeps its top-k list privately:
+// a row-major tiling (database rows on M, k2_batched.cu) each CTA stages only HALF of the query block per
+// K block — 128 database rows (raw -> x_hi, x_lo) and 128 queries (q_hi, q_lo) — which halves the L2 ->
+// shared-memory query traffic per flop, and the accumulator comes out with TMEM lane == query, so every epilogue thread owns ONE query and keeps its top-k list privately:
 // no warp collectives, no locks, a register threshold, and a warm-up that costs k*ln(256/k) scalar
 // insertions per thread instead of k warp-wide extractions per (warp, query).
 //
@@ -554,16 +554,18 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
   return cudaGetLastError();
 }
 
-// which kernel serves a batch of B: 0 = query-major pair kernel (this file), 1 = row-major pair kernel
-// (k2_pair.cu), 2 = one-CTA kernel (k2_batched.cu).  CSLAM_NNS_K2_FORCE=qm|pair|legacy overrides.
+// which kernel serves a batch of B: 0 = query-major pair kernel (this file: the MMA work is that of 256
+// queries whatever B is), 2 = row-major one-CTA kernel (k2_batched.cu: MMA N = B padded to 16, cheaper for
+// small batches).  Measured crossover on B200 (2M x 256 and 400k x 4096): between 64 and 128 queries.
+// CSLAM_NNS_K2_FORCE=qm|rows overrides (development).
 int q_route(int B) {
   static int forced = -2;
   if (forced == -2) {
     const char* v = getenv("CSLAM_NNS_K2_FORCE");
-    forced = !v ? -1 : !strcmp(v, "qm") ? 0 : !strcmp(v, "pair") ? 1 : !strcmp(v, "legacy") ? 2 : -1;
+    forced = !v ? -1 : !strcmp(v, "qm") ? 0 : (!strcmp(v, "rows") || !strcmp(v, "legacy")) ? 2 : -1;
   }
   if (forced >= 0) return forced;
-  return B > 128 ? 0 : 1;
+  return B > 96 ? 0 : 2;
 }
 
 }  // namespace
@@ -572,7 +574,6 @@ bool k2_supported(int B, int k) {
   if (B < 1 || B > kK2MaxBatch || k < 1 || k > 32) return false;
   switch (q_route(B)) {
     case 0: return (q_env_bk() == 16 ? qpick_stages<16>(k) : qpick_stages<32>(k)) >= 2;
-    case 1: return k2p_supported(B, k);
     default: return k2s_supported(B, k);
   }
 }
@@ -580,7 +581,6 @@ bool k2_supported(int B, int k) {
 int k2_parts(long long n, int B, int num_sms) {
   switch (q_route(B)) {
     case 0: return q_pairs(n, num_sms);
-    case 1: return k2p_grid(n, num_sms);
     default: return k2s_grid(n, num_sms);
   }
 }
@@ -588,7 +588,6 @@ int k2_parts(long long n, int B, int num_sms) {
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
   switch (q_route(a.B)) {
     case 0: return q_env_bk() == 16 ? qlaunch<16>(a, num_sms, stream, err) : qlaunch<32>(a, num_sms, stream, err);
-    case 1: return k2p_launch(a, num_sms, stream, err);
     default: return k2s_launch(a, num_sms, stream, err);
   }
 }

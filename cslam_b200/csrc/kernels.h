@@ -75,11 +75,8 @@ int k2_parts(long long n, int B, int num_sms);
 cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_lo, float* inv_qn,
                        cudaStream_t stream);
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err);
-// row-major CTA-pair kernel (k2_pair.cu): database rows on the MMA's M side, serves batches <= 128
-bool k2p_supported(int B, int k);
-int k2p_grid(long long n, int num_sms);
-cudaError_t k2p_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err);
-// one-CTA-per-tile predecessor (k2_batched.cu), kept selectable with CSLAM_NNS_K2_LEGACY=1 for A/B timing
+// row-major one-CTA kernel (k2_batched.cu): database rows on the MMA's M side, N = batch padded to 16;
+// serves the small batches (k2_qm.cu routes)
 bool k2s_supported(int B, int k);
 int k2s_grid(long long n, int num_sms);
 cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err);

@@ -7,7 +7,7 @@ for cfg in "$@"; do
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
-        j=json.loads(l); r=j['roofline']; print('%.3f ms  issued_frac %.3f  %s' % (r['kernel_ms'], r.get('issued_frac',0), j['clocks']['reasons']))
+        j=json.loads(l); r=j['roofline']; print('%.3f ms  issued_frac %.3f  frac %.3f %s  variant %s' % (r['kernel_ms'], r.get('issued_frac',0), r['frac'], r['bound'], j['config']['search_variant']))
     elif 'rror' in l: print(l.strip())
 "
 done
