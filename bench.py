@@ -331,6 +331,16 @@ def main():
                 "note": "achieved = N*ld*4 algorithmic bytes per launch / CUDA-event duration; peak = %s "
                         "copy bandwidth" % which}
 
+    # traffic: DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this
+    # workload (profiles/ncu_traffic.json), null when none exists for it
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.workload)
+        if tr and world == 1 and not (args.rows or args.dim or args.batch or args.k):
+            roof["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+            roof["traffic_source"] = tr["source"]
+    except Exception:
+        pass
+
     cpu = None
     if not args.no_cpu_baseline:
         v, cores, desc = cpu_port_qps(rows, dim, batch, k)
