@@ -139,10 +139,9 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   uint64_t* my_bars = bars + warp * S;
   unsigned char* my_stage = stage_base + (size_t)warp * S * p.stage_bytes;
 
-  auto issue = [&](long long item) {  // lane 0 only
-    const int s = (int)(item % S);
-    const long long tj = item / p.n_chunks;
-    const int c = (int)(item - tj * p.n_chunks);
+  // lane 0 only.  The ring slot, tile index and column chunk are tracked incrementally by the callers:
+  // a 64-bit div/mod per tile costs as much as the tile's arithmetic.
+  auto issue = [&](int s, long long tj, int c) {
     const long long row0 = (gw + tj * GW) * R;
     const float4* src;
     uint32_t bytes;
@@ -166,8 +165,16 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     for (int s = 0; s < S; ++s) mbar_init(&my_bars[s], 1);
     mbar_fence_init();
     fence_proxy_async();
-    for (int i = 0; i < S && i < my_items; ++i) issue(i);
+    long long tj = 0;
+    int c = 0;
+    for (int i = 0; i < S && i < my_items; ++i) {
+      issue(i, tj, c);
+      if (++c == p.n_chunks) { c = 0; ++tj; }
+    }
   }
+  // position of the NEXT item to issue (item index it + S while consuming item it)
+  long long nx_tile = p.n_chunks == 1 ? (long long)S : (long long)(S / p.n_chunks);
+  int nx_chunk = p.n_chunks == 1 ? 0 : S % p.n_chunks;
   u64* my_list = lists + (size_t)warp * p.k;
   if (p.k > 32) warp_list_clear(my_list, p.k, lane);
   u64 thr = 0ull, mine = 0ull;
@@ -203,9 +210,9 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     part = group_sum(part, lpr);
     const float inv_qn = 1.0f / fmaxf(sqrtf(part), kEps);
 
+    int s = 0;
+    uint32_t parity = 0;
     for (long long it = 0; it < my_items; ++it) {
-      const int s = (int)(it % S);
-      const uint32_t parity = (uint32_t)((it / S) & 1);
       const long long row0 = (gw + it * GW) * R;
       const long long rows_ll = p.n - row0;
       const int rows = rows_ll > R ? R : (int)rows_ll;
@@ -239,8 +246,9 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       __syncwarp();
       if (lane == 0 && it + S < my_items) {
         fence_proxy_async();
-        issue(it + S);
+        issue(s, it + S, 0);
       }
+      if (++s == S) { s = 0; parity ^= 1u; }
     }
   } else {
     // -- stage the query in shared memory, compute 1/max(|q|, eps) --------------------------------
@@ -264,11 +272,10 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
 
     // one row per tile, accumulated across column chunks by the whole warp
     float dot = 0.f, nn = 0.f;
+    int s = 0, c = 0;
+    uint32_t parity = 0;
+    long long tj = 0;
     for (long long it = 0; it < my_items; ++it) {
-      const int s = (int)(it % S);
-      const uint32_t parity = (uint32_t)((it / S) & 1);
-      const long long tj = it / p.n_chunks;
-      const int c = (int)(it - tj * p.n_chunks);
       const long long row = gw + tj * GW;
       int f4 = p.ld4 - c * p.chunk_f4;
       if (f4 > p.chunk_f4) f4 = p.chunk_f4;
@@ -301,11 +308,41 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       __syncwarp();
       if (lane == 0 && it + S < my_items) {
         fence_proxy_async();
-        issue(it + S);
+        issue(s, nx_tile, nx_chunk);
       }
+      if (++nx_chunk == p.n_chunks) { nx_chunk = 0; ++nx_tile; }
+      if (++c == p.n_chunks) { c = 0; ++tj; }
+      if (++s == S) { s = 0; parity ^= 1u; }
     }
   }
   if (p.all_sims) return;
+
+  // -- k == 1: the best key of the grid is one atomicMax per CTA; the CTA that draws the last ticket
+  //    decodes and publishes it.  No scratch lists, no second merge level. ------------------------------
+  if (p.k == 1) {
+    if (lane == 0) my_list[0] = thr;
+    __syncthreads();
+    if (tid == 0) {
+      u64 best = 0ull;
+#pragma unroll
+      for (int w = 0; w < W; ++w) best = lists[w] > best ? lists[w] : best;
+      u64* gbest = reinterpret_cast<u64*>(p.ticket + 2);  // zero between launches, like the ticket
+      if (best != 0ull) atomicMax(gbest, best);
+      __threadfence();
+      const unsigned t = atomicAdd(p.ticket, 1u);
+      if (t == gridDim.x - 1) {
+        __threadfence();
+        const u64 key = atomicExch(gbest, 0ull);
+        const bool have = key != 0ull;
+        const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
+        if (p.out_keys) p.out_keys[0] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
+        if (p.out_idx) p.out_idx[0] = have ? grow : -1ll;
+        if (p.out_sim) p.out_sim[0] = have ? key_sim(key) : -INFINITY;
+        *p.ticket = 0u;
+      }
+    }
+    return;
+  }
 
   // -- CTA merge -> scratch ---------------------------------------------------------------------
   u64* cta_out = reinterpret_cast<u64*>((reinterpret_cast<uintptr_t>(flag + 2) + 7) & ~(uintptr_t)7);  // [k]
