@@ -343,7 +343,7 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->num_sms = sms;
   h->initial = initial_capacity > 0 ? initial_capacity : 1000;
   h->k1.stage_bytes = env_int("CSLAM_K1_STAGE_BYTES", 8192);
-  h->k1.stages = env_int("CSLAM_K1_STAGES", 3);
+  h->k1.stages = env_int("CSLAM_K1_STAGES", 2);  // 8 KB x 2 per warp: best of the B200 sweep (profiles/r1_k1_sweep_v2.log)
   h->k1.ctas = env_int("CSLAM_K1_CTAS", 0);
   h->variant = env_int("CSLAM_NNS_VARIANT", 0);
   *out = h;
