@@ -342,6 +342,8 @@ def main():
         if tr and world == 1 and not (args.rows or args.dim or args.batch or args.k):
             roof["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
             roof["traffic_source"] = tr["source"]
+            if "tensor_pipe_active_pct" in tr:   # sm__pipe_tensor_cycles_active, same capture
+                roof["tensor_pipe_active_pct_ncu"] = tr["tensor_pipe_active_pct"]
     except Exception:
         pass
 

@@ -11,8 +11,9 @@
 // no warp collectives, no locks, a register threshold, and a warm-up that costs k*ln(256/k) scalar
 // insertions per thread instead of k warp-wide extractions per (warp, query).
 //
-//   warp  roles (384 threads per CTA; both CTAs run every role except the MMA issue)
-//   0-3   epilogue   thread t <-> query 128*rank + t: tcgen05.ld 32 columns (= database rows) at a time,
+//   warp  roles (512 threads per CTA; both CTAs run every role except the MMA issue)
+//   0-3, 12-15  epilogue   thread <-> query 128*rank + t and one half of the 256 columns (warps 0-3 columns
+//                    0..127, warps 12-15 columns 128..255): tcgen05.ld 32 columns (= database rows) at a time,
 //                    s = (acc + mean(q) * sum(x)) * inv|x| * inv|q|, compare with the thread's threshold,
 //                    insert into the thread's sorted list (shared memory, [k][128] so lanes never conflict)
 //   4     X producer  TMA of this CTA's 128 database rows (L2 evict-first)
@@ -39,7 +40,7 @@ namespace {
 
 constexpr int BM = 128;   // queries per CTA (MMA M = 256 over the pair) and database rows per CTA and tile
 constexpr int BN2 = 256;  // database rows per super tile (MMA N)
-constexpr int kThreads = 384;
+constexpr int kThreads = 512;  // warps 0-3 and 12-15 epilogue, 4 X producer, 5 MMA, 6 Q producer, 8-11 converter
 constexpr int kTmemCols = 512;
 constexpr int kMaxStages = 12;
 
@@ -50,7 +51,7 @@ struct QDev {
   uint32_t idesc;
   const float* inv_qn;
   const float* q_mean;
-  u64* part_keys;  // [pairs][B][k]
+  u64* part_keys;  // [2 * pairs][B][k]
   u64* prof;
 };
 
@@ -68,7 +69,7 @@ __host__ __device__ inline QSmem qcarve(int k, int stages) {
   s.q_lo_off = 3 * s.tile_bytes;
   s.stage_bytes = 4 * s.tile_bytes;  // 16 KB (BK = 32) or 8 KB (BK = 16) per tile: multiple of 1024
   uint32_t o = s.stage_bytes * (uint32_t)stages;
-  s.lists_off = o;  o += (uint32_t)BM * k * 8;         // [k][128] keys
+  s.lists_off = o;  o += 2u * BM * k * 8;              // [2 column halves][k][128] keys
   s.norm_off = o;   o += 2u * 2u * BN2 * 4;            // [2 accumulators][inv|x| (256), sum(x) (256)]
   s.bars_off = o;   o += (4u * kMaxStages + 10u) * 8;
   s.tmem_off = o;   o += 16;
@@ -131,20 +132,40 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)
     }                                           \
   } while (0)
 
-// Thread-private insertion into a descending list stored with stride 128 (entry j of this thread at lst[j * 128]).
-// Returns the new threshold (similarity of the k-th entry once the list is full).
-__device__ __noinline__ float private_insert(u64* lst, int k, u64 key, float thr) {
-  if (key <= lst[(k - 1) * BM]) return thr;
-  int j = k - 1;
-  while (j > 0) {
-    const u64 up = lst[(j - 1) * BM];
-    if (up >= key) break;
-    lst[j * BM] = up;
-    --j;
+// State of one thread-private list, passed and returned BY VALUE so that it stays in registers across the
+// out-of-line call (inlining the insertion 32x per chunk blew the epilogue up to ~15k instructions and the
+// instruction cache with it: C5 went from 5.9 to 15.5 ms).
+struct TopState {
+  int cnt, min_pos;
+  u64 min_key;
+  float thr, thr_u;
+};
+__device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq, TopState st) {
+  if (st.cnt < k) {
+    lst[st.cnt * BM] = key;
+    if (++st.cnt < k) return st;
+  } else {
+    if (key <= st.min_key) return st;
+    lst[st.min_pos * BM] = key;
   }
-  lst[j * BM] = key;
-  const u64 kth = lst[(k - 1) * BM];
-  return kth != 0ull ? key_sim(kth) : thr;
+  u64 mk = ~0ull;
+  int mp = 0;
+  for (int j = 0; j < k; j += 4) {
+    const u64 e0 = lst[j * BM];
+    const u64 e1 = j + 1 < k ? lst[(j + 1) * BM] : ~0ull;
+    const u64 e2 = j + 2 < k ? lst[(j + 2) * BM] : ~0ull;
+    const u64 e3 = j + 3 < k ? lst[(j + 3) * BM] : ~0ull;
+    if (e0 < mk) { mk = e0; mp = j; }
+    if (e1 < mk) { mk = e1; mp = j + 1; }
+    if (e2 < mk) { mk = e2; mp = j + 2; }
+    if (e3 < mk) { mk = e3; mp = j + 3; }
+  }
+  st.min_key = mk;
+  st.min_pos = mp;
+  st.thr = key_sim(mk);
+  const float t_ = st.thr / invq;
+  st.thr_u = t_ - fabsf(t_) * 4.8e-7f;
+  return st;
 }
 
 template <int BK>
@@ -173,7 +194,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
   uint64_t* norm_bar = acc_full + 4;             // [2] local: all 256 rows' norms are in (8 converter warps)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
 
-  for (int i = tid; i < BM * p.k; i += kThreads) lists[i] = 0ull;
+  for (int i = tid; i < 2 * BM * p.k; i += kThreads) lists[i] = 0ull;
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -183,7 +204,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
-      mbar_init(&acc_empty[a], 8);
+      mbar_init(&acc_empty[a], 16);
       mbar_init(&norm_bar[a], 8);
     }
     mbar_fence_init();
@@ -275,7 +296,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
         p.prof[blockIdx.x * 16 + 4] = (u64)w2;
       }
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 8 && warp < 12) {
     // ===== converter ===============================================================================
     const int r = tid - 8 * 32;  // row of this CTA's 128-row tile
     constexpr int kChunks = BK / 4;  // 16-byte chunks per row
@@ -336,15 +357,27 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       p.prof[blockIdx.x * 16 + 11] = (u64)wce;
       p.prof[blockIdx.x * 16 + 12] = (u64)wcf;
     }
-  } else if (warp < 4) {
-    // ===== epilogue: thread <-> query ===============================================================
-    const int q = (int)rank * BM + tid;
+  } else if (warp < 4 || warp >= 12) {
+    // ===== epilogue: thread <-> (query, half of the super tile's 256 columns) ========================
+    // Warp w may only touch TMEM lanes 32 (w % 4) .. +31, so warps 0-3 take columns 0..127 and warps 12-15
+    // columns 128..255 of the same 128 queries: two private lists per query, merged by K4 like any other part.
+    const int eh = warp >= 12 ? 1 : 0;
+    const int tq = (warp & 3) * 32 + lane;
+    const int q = (int)rank * BM + tq;
     const bool valid = q < p.B;
     const float qmean_r = valid ? p.q_mean[q] : 0.f;
     const float invq_r = valid ? p.inv_qn[q] : 0.f;
-    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-    u64* lst = lists + tid;
-    float thr = -INFINITY;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    u64* lst = lists + (size_t)eh * BM * p.k + tq;
+    // Thread-private UNSORTED top-k: the first k candidates fill the list, after that a candidate replaces
+    // the smallest entry and the minimum is re-found with k independent loads (a sorted list costs a
+    // dependent load-compare-store chain per shifted entry; K4 does not need sorted parts).
+    TopState ts;
+    ts.cnt = 0;
+    ts.min_pos = 0;
+    ts.min_key = 0ull;
+    ts.thr = -INFINITY;    // similarity of the smallest entry once the list is full
+    ts.thr_u = -INFINITY;  // the same bound for u = s / inv|q| (saves a multiply per column), 2^-21 slack
     long long wepi = 0, wnorm = 0, wfence = 0, wscan = 0;
     for (long long t = 0; t < my_tiles; ++t) {
       const int a = (int)(t & 1);
@@ -358,7 +391,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       const long long tscan0 = p.prof ? clock64() : 0;
       const float* ninv = norms + a * (2 * BN2);
       const float* nsum = ninv + BN2;
-      for (int c0 = 0; c0 < BN2; c0 += 32) {
+      for (int c0 = eh * (BN2 / 2); c0 < (eh + 1) * (BN2 / 2); c0 += 32) {
         if (c0 >= valid_cols || (p.dbg & 4)) break;
         uint32_t v[32];
         if (!(p.dbg & 32)) {
@@ -379,23 +412,29 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           const float sm_[4] = {sm.x, sm.y, sm.z, sm.w};
 #pragma unroll
           for (int jj = 0; jj < 4; ++jj) {
-            const float s_ = fmaf(qmean_r, sm_[jj], __uint_as_float(v[j4 + jj])) * iv_[jj] * invq_r;
-            v[j4 + jj] = __float_as_uint(s_);
+            const float u_ = fmaf(qmean_r, sm_[jj], __uint_as_float(v[j4 + jj])) * iv_[jj];
+            v[j4 + jj] = __float_as_uint(u_);
             // ties go to the exact key comparison (a lower row index wins); NaN passes and sorts first
-            m |= (!(s_ < thr) && c0 + j4 + jj < valid_cols) ? (1u << (j4 + jj)) : 0u;
+            m |= (!(u_ < ts.thr_u) && c0 + j4 + jj < valid_cols) ? (1u << (j4 + jj)) : 0u;
           }
         }
         if (!valid || (p.dbg & 16)) m = 0u;
         const uint32_t um = __reduce_or_sync(kFull, m);
-        if (um != 0u) {  // rare after warm-up; the branches below are warp-uniform
+        if (um != 0u) {  // the branches on `um` are warp-uniform
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (um & (1u << j)) {
-              if (m & (1u << j))
-                thr = private_insert(lst, p.k,
-                                     ((u64)sim_to_ord(__uint_as_float(v[j])) << 32) |
-                                         (u64)(~(uint32_t)(row_base + c0 + j)),
-                                     thr);
+          for (int g8 = 0; g8 < 32; g8 += 8) {
+            if ((um >> g8) & 0xffu) {
+#pragma unroll
+              for (int j = g8; j < g8 + 8; ++j) {
+                if (um & (1u << j)) {
+                  if (m & (1u << j)) {
+                    const float s_ = __uint_as_float(v[j]) * invq_r;
+                    if (!(s_ < ts.thr))
+                      ts = offer_key(lst, p.k, ((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)),
+                                     invq_r, ts);
+                  }
+                }
+              }
             }
           }
         }
@@ -414,9 +453,9 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       p.prof[blockIdx.x * 16 + 9] = (u64)wfence;
       p.prof[blockIdx.x * 16 + 10] = (u64)wscan;
     }
-    // this CTA's 128 queries -> part_keys[pair][q][k]
+    // this thread's list -> part_keys[2 * pair + column half][q][k]
     if (valid) {
-      u64* out = p.part_keys + ((size_t)pair * p.B + q) * p.k;
+      u64* out = p.part_keys + ((size_t)(2 * pair + eh) * p.B + q) * p.k;
       for (int j = 0; j < p.k; ++j) out[j] = lst[j * BM];
     }
   }
@@ -580,7 +619,7 @@ bool k2_supported(int B, int k) {
 
 int k2_parts(long long n, int B, int num_sms) {
   switch (q_route(B)) {
-    case 0: return q_pairs(n, num_sms);
+    case 0: return 2 * q_pairs(n, num_sms);
     default: return k2s_grid(n, num_sms);
   }
 }

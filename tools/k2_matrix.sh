@@ -3,7 +3,7 @@
 w=$1; rows=$2; shift 2
 for cfg in "$@"; do
   printf "%-60s " "$cfg"
-  env $cfg timeout 300 python bench.py --workload $w --rows $rows $EXTRA --steps 5 --no-cpu-baseline --no-e2e 2>&1 | python -c "
+  env $cfg timeout 90 python bench.py --workload $w --rows $rows $EXTRA --steps 5 --no-cpu-baseline --no-e2e 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
