@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + ["sc"])
     ap.add_argument("--rows", type=int, default=0, help="override the row count (debugging only)")
     ap.add_argument("--dim", type=int, default=0, help="override the descriptor size (debugging only)")
     ap.add_argument("--batch", type=int, default=0, help="override the batch size (debugging only)")
@@ -179,8 +179,67 @@ def workload_config(args, rows, dim, batch, k):
             "l2": "database (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (rows * dim * 4 / 1e9)}
 
 
+def bench_scancontext(args):
+    """ScanContextMatching.search through the public Python API (host query in, host result
+    out), next to the oracle port of the reference on the host (numpy; the reference itself additionally
+    rebuilds a KD-tree per search).  One step = one search."""
+    import numpy as np
+    import torch
+    import synth
+    from cslam_b200 import _native
+    from cslam_b200.lidar_pr import ScanContextMatching
+    from oracle import sc_oracle
+    n = args.rows or 50_000
+    torch.cuda.set_device(0)
+    lib = _native.load()
+    base = synth.scancontexts(61, 2000)
+    m = ScanContextMatching()
+    rng = np.random.default_rng(7)
+    for i in range(n):   # distinct descriptors: a base scan, rolled and scaled
+        m.add_item(np.roll(base[i % 2000].reshape(20, 60), i // 2000, axis=1) * (1.0 + 1e-3 * (i // 2000)), i)
+    qs = synth.sc_queries_for(1061, base, 64)
+    for j in range(args.warmup):
+        m.search(qs[j % 64], 1)
+    torch.cuda.synchronize()
+    l0 = lib.cslam_nns_launch_count()
+    t0 = time.perf_counter()
+    for j in range(args.steps):
+        m.search(qs[j % 64], 1)
+    dt = time.perf_counter() - t0
+    launches = lib.cslam_nns_launch_count() - l0
+    # CPU: the oracle on a bounded sample of the same database (cost is linear in rows for step 1 and
+    # constant for step 2, so it is NOT scaled: the sample is stated)
+    ns = min(n, 20000)
+    db = np.stack([np.roll(base[i % 2000].reshape(20, 60), i // 2000, axis=1).reshape(-1) for i in range(ns)])
+    items = {i: i for i in range(ns)}
+    t1 = time.perf_counter()
+    reps = 3
+    for j in range(reps):
+        sc_oracle.search(db, items, qs[j])
+    cpu = reps / (time.perf_counter() - t1)
+    hbm_peak, _, _, which = measured_peaks()
+    bytes_ = n * 20 * 8 + 10 * 1200 * 8
+    line = {"metric": "ScanContext searches/s (ring-key shortlist of 10 + column-shift distance)",
+            "value": args.steps / dt, "unit": "searches/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "SURVEY 8 f4: ScanContextMatching.search, %d x (20 x 60) float64 database" % n,
+                       "rows": n, "l2": "latency-bound at SLAM sizes: 2 kernels + 1 H2D + 2 D2H per search"},
+            "roofline": {"bound": "hbm", "achieved": bytes_ / (dt / args.steps) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": bytes_ / (dt / args.steps) / 1e9 / hbm_peak, "traffic": None,
+                         "note": "algorithmic bytes = ring keys n*20*8 + 10 candidates * 9.6 KB; the call is "
+                                 "latency-bound (host round trip), the fraction is reported for completeness"},
+            "cpu_baseline": {"value": cpu, "unit": "searches/s", "cores": 1, "kind": "port",
+                             "sample": "%d searches over the first %d rows with oracle/sc_oracle.py (numpy, 1 thread)" % (reps, ns)},
+            "e2e": {"value": args.steps / dt, "unit": "searches/s", "h2d_bytes_per_step": 1220 * 8, "d2h_bytes_per_step": 200},
+            "gpu_launches": int(launches)}
+    print(json.dumps(line))
+
+
 def main():
     args = parse()
+    if args.workload == "sc":
+        return bench_scancontext(args)
     rows, dim, batch, k, _ = WORKLOADS[args.workload]
     if args.rows:
         rows = args.rows

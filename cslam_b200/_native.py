@@ -50,6 +50,19 @@ SIGNATURES = {
                                          _c.c_void_p, _c.POINTER(_c.c_float)]),
 }
 
+# include/cslam_scancontext.h (ScanContext matcher)
+_f64p = _c.c_void_p
+SC_SIGNATURES = {
+    "cslam_sc_last_error": (_c.c_char_p, [_handle]),
+    "cslam_sc_create": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _i64, _c.POINTER(_handle)]),
+    "cslam_sc_destroy": (_c.c_int, [_handle]),
+    "cslam_sc_size": (_i64, [_handle]),
+    "cslam_sc_add": (_c.c_int, [_handle, _f64p, _f64p, _c.c_void_p, _c.POINTER(_i64)]),
+    "cslam_sc_search": (_c.c_int, [_handle, _f64p, _f64p, _i64p, _f64p, _c.c_void_p, _c.c_void_p]),
+    "cslam_sc_descriptors_ptr": (_c.c_void_p, [_handle]),
+    "cslam_sc_ringkeys_ptr": (_c.c_void_p, [_handle]),
+}
+
 _lib = None
 
 
@@ -72,7 +85,7 @@ def load():
             "(or `python -c 'import __graft_entry__ as g; g.build()'`). "
             "cslam_b200 has no CPU or PyTorch fallback.")
     lib = ctypes.CDLL(LIB_PATH)
-    for name, (res, args) in SIGNATURES.items():
+    for name, (res, args) in list(SIGNATURES.items()) + list(SC_SIGNATURES.items()):
         fn = getattr(lib, name)  # AttributeError here == header/library mismatch
         fn.restype = res
         fn.argtypes = args

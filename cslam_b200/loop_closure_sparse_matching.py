@@ -64,14 +64,15 @@ class LoopClosureSparseMatching(object):
     def __init__(self, params, node=None, candidate_selector=None):
         self.params = params
         self.node = node
-        if self.params.get("frontend.sensor_type", "stereo") == "lidar":
-            raise NotImplementedError(
-                "lidar uses ScanContextMatching in the reference (:22-23), which is out of scope")
-        self.local_nnsm = NearestNeighborsMatching()
+        lidar = self.params.get("frontend.sensor_type", "stereo") == "lidar"
+        if lidar:  # reference :22-23,29-30: the ScanContext matcher implements the same three methods
+            from .lidar_pr import ScanContextMatching
+        make = ScanContextMatching if lidar else NearestNeighborsMatching
+        self.local_nnsm = make()
         self.other_robots_nnsm = {}
         for i in range(self.params['max_nb_robots']):
             if i != self.params['robot_id']:
-                self.other_robots_nnsm[i] = NearestNeighborsMatching()
+                self.other_robots_nnsm[i] = make()
         if candidate_selector is not None:
             self.candidate_selector = candidate_selector
         elif _HAVE_REFERENCE_SELECTOR:
@@ -121,6 +122,8 @@ class LoopClosureSparseMatching(object):
         msgs = list(msgs)
         if not msgs:
             return []
+        if not hasattr(self.local_nnsm, "search_batch"):  # lidar: the ScanContext matcher is single-query
+            return [self.add_other_robot_global_descriptor(m) for m in msgs]
         block = np.stack([np.asarray(m.descriptor).astype(np.float32) for m in msgs])
         by_robot = {}
         for j, m in enumerate(msgs):

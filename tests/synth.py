@@ -49,3 +49,31 @@ def queries_for(seed, db, nq, dist="rand", every=3, noise=0.05):
         v = db[(7 * j + 1) % n] + noise * eps[j]
         qs[j] = v / np.linalg.norm(v)
     return qs
+
+
+def scancontexts(seed, n, shape=(20, 60), empty_frac=0.15):
+    """(n, rings*sectors) float64 ScanContext-like descriptors: non-negative "max heights" with a share of
+    empty bins and a few completely empty sectors (columns), as ptcloud2sc produces for real scans
+    (reference cslam/lidar_pr/scancontext_utils.py:45-73)."""
+    r, s = shape
+    h = 4.0 * uniform(seed, (n, r, s))
+    hole = uniform(seed + 101, (n, r, s)) < empty_frac
+    h[hole] = 0.0
+    dead = uniform(seed + 202, (n, 1, s)) < 0.08          # sectors with no return at all
+    h = np.where(dead, 0.0, h)
+    return h.reshape(n, r * s)
+
+
+def sc_queries_for(seed, db, nq, shape=(20, 60), every=2, noise=0.05):
+    """Queries: fresh descriptors, every `every`-th one a DB scan seen again under a yaw rotation (a column
+    roll) with a little height noise — the case the column-shift distance exists for."""
+    r, s = shape
+    n = db.shape[0]
+    qs = scancontexts(seed, nq, shape)
+    eps = normal(seed + 77, (nq, r, s))
+    for j in range(0, nq, every):
+        src = db[(5 * j + 3) % n].reshape(r, s)
+        rolled = np.roll(src, (7 * j + 1) % s, axis=1)
+        v = np.where(rolled > 0, np.maximum(rolled + noise * eps[j], 0.0), 0.0)
+        qs[j] = v.reshape(-1)
+    return qs
