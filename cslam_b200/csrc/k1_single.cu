@@ -76,9 +76,11 @@ __device__ __forceinline__ float cos_fast(float dot, float nn, float inv_qn) {
 
 // Per-warp running top-k.  k == 1: the best key is the register `thr`.  k <= 32: lane j holds the
 // j-th best key in `mine` (sorted descending, 0 = empty).  k > 32: sorted list in shared memory.
+// `floor` (optional): a proven lower bound of the final k-th key; anything below it is dropped even
+// while the list is not full yet (used by the merge steps, where it removes most insertions).
 __device__ __forceinline__ void offer(u64* list, int k, u64 key, bool have, u64& thr, u64& mine,
-                                      int lane) {
-  unsigned m = __ballot_sync(kFull, have && key > thr);
+                                      int lane, u64 floor = 0ull) {
+  unsigned m = __ballot_sync(kFull, have && key > thr && key >= floor);
   if (m == 0) return;  // the common case after warm-up
   if (k == 1) {
     u64 best = (have && key > thr) ? key : 0ull;
@@ -344,7 +346,88 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     return;
   }
 
-  // -- CTA merge -> scratch ---------------------------------------------------------------------
+  // -- 2 <= k <= 32: register lists all the way.  Warp 0 folds the CTA's 8 warp lists into its own and
+  //    publishes them; in the CTA that draws the last ticket every warp folds 1/8 of the grid's lists
+  //    (loads batched 4 deep so the L2 round trips overlap), warp 0 folds those 8 and writes the result. ----
+  if (p.k <= 32) {
+    if (lane < p.k) my_list[lane] = mine;
+    __syncthreads();
+    if (warp == 0) {
+      // floor: the best k-th key of any warp list (k keys at or above it exist, so nothing below it
+      // can be in the CTA's top-k)
+      u64 fl = lane < W ? lists[(size_t)lane * p.k + (p.k - 1)] : 0ull;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        const u64 o = __shfl_xor_sync(kFull, fl, off);
+        fl = o > fl ? o : fl;
+      }
+      for (int base = p.k; base < W * p.k; base += 32) {
+        const int i = base + lane;
+        const u64 key = i < W * p.k ? lists[i] : 0ull;
+        offer(my_list, p.k, key, key != 0ull, thr, mine, lane, fl);
+      }
+      if (lane < p.k) p.scratch[(size_t)blockIdx.x * p.k + lane] = mine;
+      __threadfence();
+      __syncwarp();
+      unsigned t = 0;
+      if (lane == 0) t = atomicAdd(p.ticket, 1u);
+      t = __shfl_sync(kFull, t, 0);
+      if (lane == 0) *flag = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!*flag) return;
+    __threadfence();
+    const int total = (int)gridDim.x * p.k;
+    const int per_warp = (total + W - 1) / W;
+    const int lo = warp * per_warp;
+    const int hi = lo + per_warp < total ? lo + per_warp : total;
+    thr = 0ull;
+    mine = 0ull;
+    // floor: the best k-th key of any CTA list (every warp computes it; the loads are L2 hits in flight
+    // together with the first batch below)
+    u64 gfl = 0ull;
+    for (int c = lane; c < (int)gridDim.x; c += 32) {
+      const u64 v = __ldcg(p.scratch + (size_t)c * p.k + (p.k - 1));
+      gfl = v > gfl ? v : gfl;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const u64 o = __shfl_xor_sync(kFull, gfl, off);
+      gfl = o > gfl ? o : gfl;
+    }
+    for (int base = lo; base < hi; base += 128) {
+      u64 kk[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = base + u * 32 + lane;
+        kk[u] = i < hi ? __ldcg(p.scratch + i) : 0ull;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) offer(my_list, p.k, kk[u], kk[u] != 0ull, thr, mine, lane, gfl);
+    }
+    __syncthreads();  // everybody is past reading `lists` as the CTA merge's input
+    if (lane < p.k) my_list[lane] = mine;
+    __syncthreads();
+    if (warp == 0) {
+      for (int base = p.k; base < W * p.k; base += 32) {
+        const int i = base + lane;
+        const u64 key = i < W * p.k ? lists[i] : 0ull;
+        offer(my_list, p.k, key, key != 0ull, thr, mine, lane, gfl);
+      }
+      if (lane < p.k) {
+        const u64 key = mine;
+        const bool have = key != 0ull;
+        const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
+        if (p.out_keys) p.out_keys[lane] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
+        if (p.out_idx) p.out_idx[lane] = have ? grow : -1ll;
+        if (p.out_sim) p.out_sim[lane] = have ? key_sim(key) : -INFINITY;
+      }
+      if (lane == 0) *p.ticket = 0u;
+    }
+    return;
+  }
+
+  // -- 32 < k <= 128: CTA merge -> scratch ------------------------------------------------------------
   u64* cta_out = reinterpret_cast<u64*>((reinterpret_cast<uintptr_t>(flag + 2) + 7) & ~(uintptr_t)7);  // [k]
   if (p.k == 1) {
     if (lane == 0) my_list[0] = thr;

@@ -131,6 +131,45 @@ class NearestNeighborsMatching(object):
             self.items[self.n + j] = item
         self.n += len(items)
 
+    # -- wire / on-disk format (additive) ------------------------------------------------
+    def add_descriptor_msgs(self, msgs):
+        """Ingest one ``GlobalDescriptors`` message: each element carries ``descriptor`` (the float32[]
+        wire field, reference global_descriptor_loop_closure_detection.py:158-162,211-214) and
+        ``keyframe_id``.  The descriptors are packed once into pinned host memory and appended with ONE
+        DMA, instead of one list->array->tensor->H2D conversion per descriptor (reference
+        loop_closure_sparse_matching.py:64-65)."""
+        msgs = list(msgs)
+        if not msgs:
+            return
+        dim = len(msgs[0].descriptor) if self.dim is None else self.dim
+        staging = torch.empty((len(msgs), dim), dtype=torch.float32,
+                              pin_memory=torch.cuda.is_available())
+        block = staging.numpy()
+        for j, m in enumerate(msgs):
+            block[j] = np.asarray(m.descriptor, dtype=np.float32)   # raises on a wrong length
+        self.add_items(staging, [m.keyframe_id for m in msgs])
+
+    def save(self, path):
+        """Write the database (rows 0..n-1 exactly as stored, and the row -> item map) to ``path`` (.npz).
+        The reference has no persistence; this is what a restart needs."""
+        import pickle
+        rows = self.data[:self.n].cpu().numpy() if self.n else np.zeros((0, self.dim or 0), np.float32)
+        np.savez(path, data=rows, dim=np.int64(self.dim or 0),
+                 items=np.frombuffer(pickle.dumps([self.items[i] for i in range(self.n)]), dtype=np.uint8))
+
+    @classmethod
+    def load(cls, path):
+        """Rebuild a matcher from ``save``'s file: one bulk append, identical rows and items."""
+        import pickle
+        z = np.load(path if str(path).endswith(".npz") else str(path) + ".npz")
+        m = cls()
+        items = pickle.loads(z["items"].tobytes())
+        if len(items):
+            m.add_items(z["data"], items)
+        elif int(z["dim"]) > 0:
+            m.dim = int(z["dim"])
+        return m
+
     def _append(self, h, rows):
         rows = rows.contiguous()
         on_dev = rows.is_cuda

@@ -316,3 +316,28 @@ def test_no_vmm_fallback_path(M, monkeypatch):
     assert np.array_equal(m.data.cpu().numpy()[:m.n], db)
     items, sims = m.search(db[2400], 2)
     assert items[0] == 2400
+
+
+# ---- wire-format ingest and persistence ------------------------------------------------
+
+def test_message_ingest_and_save_load_round_trip(M, tmp_path):
+    GD = namedtuple("GlobalDescriptor", ["keyframe_id", "robot_id", "descriptor"])
+    db = synth.unit_rows(91, 1500, 96)
+    qs = synth.queries_for(92, db, 5)
+    one_by_one = M()
+    for i in range(len(db)):
+        one_by_one.add_item(db[i], 10 + i)
+    by_msg = M()
+    for lo in range(0, len(db), 10):   # <= 10 descriptors per message, like the reference's publisher
+        by_msg.add_descriptor_msgs([GD(10 + i, 1, db[i].tolist()) for i in range(lo, min(lo + 10, len(db)))])
+    assert by_msg.n == one_by_one.n and by_msg.items == one_by_one.items
+    assert torch.equal(by_msg.data[:by_msg.n].cpu(), one_by_one.data[:one_by_one.n].cpu())
+    path = str(tmp_path / "db.npz")
+    by_msg.save(path)
+    back = M.load(path)
+    assert back.n == by_msg.n and back.items == by_msg.items and back.dim == by_msg.dim
+    assert torch.equal(back.data[:back.n].cpu(), by_msg.data[:by_msg.n].cpu())
+    for q in qs:
+        a, sa = one_by_one.search(q, 10)
+        b, sb = back.search(q, 10)
+        assert a == b and np.array_equal(sa, sb)
