@@ -252,7 +252,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
   for (long long b0 = 0; b0 < B; b0 += kK2MaxBatch) {
     const int Bc = (int)((B - b0) > kK2MaxBatch ? kK2MaxBatch : (B - b0));
     const int grid = k2_parts(h->n, Bc, h->num_sms);
-    if (!h->q_lo.ensure((size_t)2 * Bc * q_ld * 4) || !h->inv_qn.ensure((size_t)2 * Bc * 4) ||
+    if (!h->q_lo.ensure((size_t)2 * Bc * q_ld * 4) || !h->inv_qn.ensure((size_t)3 * Bc * 4) ||
         !h->part_keys.ensure((size_t)grid * Bc * k_run * 8))
       return fail(h, CSLAM_NNS_ENOMEM, "batched scratch");
     const float* qc = dq + b0 * q_ld;

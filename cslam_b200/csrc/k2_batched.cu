@@ -362,6 +362,8 @@ __global__ void k2_prepare_kernel(const float* __restrict__ q, int dim, int q_ld
     const float c = u / (float)dim;
     mean_s = (c == c && fabsf(c) < 3.0e38f) ? c : 0.f;  // NaN/Inf queries: no centring
     q_mean[b] = mean_s;
+    // third plane: the grid-wide per-query lower bound of the k-th best similarity (ordered-uint), 0 = none yet
+    reinterpret_cast<unsigned*>(q_mean + gridDim.x)[b] = 0u;
   }
   __syncthreads();
   const float c = mean_s;
@@ -415,7 +417,7 @@ int k2s_grid(long long n, int num_sms) {
 // q_lo buffer layout: [q_hi plane (B x q_ld)][q_lo plane (B x q_ld)] — callers size it 2x
 cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_planes, float* inv_qn,
                        cudaStream_t stream) {
-  // inv_qn buffer layout: [inv_qn (B)][q_mean (B)] — callers size it 2x
+  // inv_qn buffer layout: [inv_qn (B)][q_mean (B)][shared threshold (B, u32)] — callers size it 3x
   k2_prepare_kernel<<<B, 128, 0, stream>>>(q, dim, q_ld, q_planes, q_planes + (size_t)B * q_ld, inv_qn,
                                           inv_qn + B);
   count_launch();

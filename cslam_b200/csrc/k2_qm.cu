@@ -51,6 +51,7 @@ struct QDev {
   uint32_t idesc;
   const float* inv_qn;
   const float* q_mean;
+  unsigned* gthr;  // [B] grid-wide lower bound of each query's k-th best similarity (ordered uint), 0 = none
   u64* part_keys;  // [2 * pairs][B][k]
   u64* prof;
 };
@@ -138,9 +139,17 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)
 struct TopState {
   int cnt, min_pos;
   u64 min_key;
-  float thr, thr_u;
+  float thr;      // similarity below which a candidate cannot matter: max(own smallest entry once the list
+                  // is full, best bound published by any list of this query)
+  float thr_u;    // the same bound for u = s / inv|q| (saves a multiply per column), 2^-21 slack
+  unsigned g_seen;  // last published bound seen (ordered uint)
 };
-__device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq, TopState st) {
+__device__ __forceinline__ void top_set_threshold(TopState& st, float thr, float invq) {
+  st.thr = thr;
+  const float t_ = thr / invq;
+  st.thr_u = t_ - fabsf(t_) * 4.8e-7f;
+}
+__device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq, unsigned* gthr, TopState st) {
   if (st.cnt < k) {
     lst[st.cnt * BM] = key;
     if (++st.cnt < k) return st;
@@ -162,9 +171,13 @@ __device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq,
   }
   st.min_key = mk;
   st.min_pos = mp;
-  st.thr = key_sim(mk);
-  const float t_ = st.thr / invq;
-  st.thr_u = t_ - fabsf(t_) * 4.8e-7f;
+  // the list is full: its smallest entry is a proven lower bound of the query's final k-th best
+  const unsigned ord = (unsigned)(mk >> 32);
+  if (ord > st.g_seen && ord != 0xffffffffu) {  // NaN entries are never a bound
+    if (gthr) atomicMax(gthr, ord);
+    st.g_seen = ord;
+    top_set_threshold(st, key_sim(mk), invq);
+  }
   return st;
 }
 
@@ -376,14 +389,28 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     ts.cnt = 0;
     ts.min_pos = 0;
     ts.min_key = 0ull;
-    ts.thr = -INFINITY;    // similarity of the smallest entry once the list is full
-    ts.thr_u = -INFINITY;  // the same bound for u = s / inv|q| (saves a multiply per column), 2^-21 slack
+    ts.thr = -INFINITY;
+    ts.thr_u = -INFINITY;
+    ts.g_seen = 0u;
+    // Grid-wide threshold sharing.  The 2 x 74 lists of a query each warm up from nothing; whenever one of
+    // them is full its smallest entry is a proven lower bound of the query's final k-th best (k real rows
+    // at or above it exist), so it is published with one atomicMax (inside offer_key) and every list of the
+    // query — full or not — drops candidates below the best bound published so far (read once per tile).
+    // This removes most of the k ln(rows/k) insertions per list, which diverge lane by lane.
+    unsigned* gq = (valid && !(p.dbg & 64)) ? p.gthr + q : nullptr;
     long long wepi = 0, wnorm = 0, wfence = 0, wscan = 0;
     for (long long t = 0; t < my_tiles; ++t) {
       const int a = (int)(t & 1);
       const uint32_t ph = (uint32_t)((t >> 1) & 1);
       const long long row_base = (pair + t * npairs) * (long long)BN2;
       const int valid_cols = (int)((p.n - row_base) < BN2 ? (p.n - row_base) : BN2);
+      if (gq) {
+        const unsigned g = __ldcg(gq);
+        if (g > ts.g_seen) {
+          ts.g_seen = g;
+          top_set_threshold(ts, ord_to_sim(g), invq_r);
+        }
+      }
       QPROF_WAIT(wnorm, mbar_wait(&norm_bar[a], ph));
       QPROF_WAIT(wfence, fence_acq_rel_cluster());  // the peer's half of norms[a] came through st.shared::cluster
       QPROF_WAIT(wepi, mbar_wait(&acc_full[a], ph));
@@ -431,7 +458,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
                     const float s_ = __uint_as_float(v[j]) * invq_r;
                     if (!(s_ < ts.thr))
                       ts = offer_key(lst, p.k, ((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)),
-                                     invq_r, ts);
+                                     invq_r, gq, ts);
                   }
                 }
               }
@@ -540,6 +567,7 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
   p.kblocks = (a.dim + BK - 1) / BK;
   p.inv_qn = a.inv_qn;
   p.q_mean = a.inv_qn + a.B;
+  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn + 2 * a.B));  // zeroed by k2_prepare
   p.part_keys = a.part_keys;
   // kind::tf32, fp32 accumulate, K-major operands; N>>3 at bit 17, M>>4 at bit 24 (M = 256 over the pair)
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN2 >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
