@@ -5,6 +5,7 @@ reference and (b) the CPU oracle on the same seeded inputs.
 Parity rule: indices equal to the reference's, except where the reference's own
 neighbouring similarities are closer than the tolerance; similarities within 1e-5*|s| + 1e-6.
 """
+import os
 from collections import namedtuple
 
 import numpy as np
@@ -341,3 +342,46 @@ def test_message_ingest_and_save_load_round_trip(M, tmp_path):
         a, sa = one_by_one.search(q, 10)
         b, sb = back.search(q, 10)
         assert a == b and np.array_equal(sa, sb)
+
+
+# ---- both batched tilings on every shape --------------------------------------------------------------
+
+@pytest.mark.parametrize("route", ["qm", "rows"])
+def test_both_batched_kernels_on_all_shapes(route):
+    """The batch-size router (k2_qm.cu: q_route) normally sends <= 96 queries to the row-major kernel and
+    more to the query-major CTA-pair kernel; here each kernel is forced (the switch is read once per process,
+    hence the subprocess) over shapes that cover padding on every axis: n < 256 and not a multiple of 256,
+    dim not a multiple of 32, B = 2 .. 256, k = 1 .. 32."""
+    import subprocess
+    import sys
+    from conftest import ROOT
+    shapes = ["300,32,4,3", "1000,128,16,10", "5000,100,37,10", "20000,256,256,10", "3000,4096,64,5",
+              "70000,512,200,1", "129,36,2,32", "257,40,97,7", "4096,64,255,32", "777,200,130,10"]
+    if route == "rows":   # the row-major kernel's shared-memory lists bound batch * k
+        shapes = [s for s in shapes if s != "4096,64,255,32"]
+    env = dict(os.environ, CSLAM_NNS_K2_FORCE=route)
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "k2_check.py")] + shapes, env=env,
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "K2 CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_batched_nan_zero_and_duplicate_rows(M):
+    """Rows that are NaN (sort first, like torch.argsort descending), all-zero (similarity 0) and exact
+    duplicates (the lower row wins) through the query-major kernel (B = 128 > 96)."""
+    n, d, B, k = 3000, 64, 128, 6
+    db = synth.unit_rows(71, n, d)
+    db[5] = np.nan
+    db[7] = 0.0
+    db[100] = db[50]
+    db[2000] = db[50]
+    qs = synth.queries_for(72, db, B)
+    qs[3] = db[50]
+    m = M()
+    m.add_items(db, list(range(n)))
+    items, sims = m.search_batch(qs, k)
+    for j in range(B):
+        assert items[j][0] == 5 and np.isnan(sims[j][0])            # the NaN row first
+        ref_items, ref_sims = m.search(qs[j], k)                     # single-query kernel
+        assert items[j] == ref_items
+        np.testing.assert_allclose(sims[j][1:], ref_sims[1:], rtol=RTOL, atol=ATOL)
+    assert items[3][1:4] == [50, 100, 2000]                          # duplicates: lower row first
