@@ -119,6 +119,17 @@ class ShardedNearestNeighborsMatching(object):
         """Device in, device out: (global rows int64 [B,k], sims f32 [B,k]); -1/-inf past the end."""
         q_dev = q_dev.contiguous()
         B = int(q_dev.shape[0])
+        if self.world == 1 and self.local._h is not None and self.local.n >= k:
+            # one shard: nothing to exchange or merge — the kernels write (row, sim) themselves
+            if out_idx is None:
+                out_idx = torch.empty((B, k), dtype=torch.int64, device=q_dev.device)
+                out_sim = torch.empty((B, k), dtype=torch.float32, device=q_dev.device)
+            h = self.local._h
+            rc = h.lib.cslam_nns_search(h.h, ctypes.c_void_p(q_dev.data_ptr()), B, q_dev.shape[1], 1, k,
+                                        ctypes.c_void_p(out_idx.data_ptr()), ctypes.c_void_p(out_sim.data_ptr()),
+                                        1, self.local._stream(), None)
+            _native.check(rc, h.h)
+            return out_idx, out_sim
         keys = self.search_keys_device(q_dev, k)
         if self.world > 1:
             gathered = torch.empty((self.world, B, k), dtype=torch.int64, device=q_dev.device)
