@@ -149,7 +149,21 @@ __device__ __forceinline__ void top_set_threshold(TopState& st, float thr, float
   const float t_ = thr / invq;
   st.thr_u = t_ - fabsf(t_) * 4.8e-7f;
 }
+// v[j] for a lane-dependent j without local memory: a 5-level select tree (31 selects)
+__device__ __forceinline__ uint32_t select32(const uint32_t (&v)[32], int j) {
+  uint32_t a[16], b[8], c[4];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) b[i] = (j & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[2 * i + 1] : b[2 * i];
+  const uint32_t d0 = (j & 8) ? c[1] : c[0], d1 = (j & 8) ? c[3] : c[2];
+  return (j & 16) ? d1 : d0;
+}
+// Called by all 32 lanes together, each with its own list and candidate (key 0 = nothing to offer).
 __device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq, unsigned* gthr, TopState st) {
+  if (key == 0ull) return st;
   if (st.cnt < k) {
     lst[st.cnt * BM] = key;
     if (++st.cnt < k) return st;
@@ -446,24 +460,19 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           }
         }
         if (!valid || (p.dbg & 16)) m = 0u;
-        const uint32_t um = __reduce_or_sync(kFull, m);
-        if (um != 0u) {  // the branches on `um` are warp-uniform
-#pragma unroll
-          for (int g8 = 0; g8 < 32; g8 += 8) {
-            if ((um >> g8) & 0xffu) {
-#pragma unroll
-              for (int j = g8; j < g8 + 8; ++j) {
-                if (um & (1u << j)) {
-                  if (m & (1u << j)) {
-                    const float s_ = __uint_as_float(v[j]) * invq_r;
-                    if (!(s_ < ts.thr))
-                      ts = offer_key(lst, p.k, ((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)),
-                                     invq_r, gq, ts);
-                  }
-                }
-              }
-            }
-          }
+        // slow path, CONVERGENT: every lane pops its own next survivor (its value is picked out of the 32
+        // registers by a select tree) and all lanes run the insertion together, each on its own list; a lane
+        // without a survivor rides along with key 0.  Rounds per chunk = the largest survivor count of any
+        // lane (1-2 after warm-up), where a branch per column served one lane at a time.
+        while (__any_sync(kFull, m != 0u)) {
+          const int j = m != 0u ? __ffs(m) - 1 : 0;
+          const bool has = m != 0u;
+          m &= m - 1u;
+          const float s_ = __uint_as_float(select32(v, j)) * invq_r;
+          const u64 key = (has && !(s_ < ts.thr))
+                              ? (((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)))
+                              : 0ull;
+          ts = offer_key(lst, p.k, key, invq_r, gq, ts);
         }
       }
       if (p.prof) wscan += clock64() - tscan0;
