@@ -279,7 +279,8 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
     if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch", e);
     CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run,
                    o_keys ? o_keys + b0 * k_run : nullptr, o_idx ? o_idx + b0 * k_run : nullptr,
-                   o_sim ? o_sim + b0 * k_run : nullptr, idx_stride, idx_offset, stream));
+                   o_sim ? o_sim + b0 * k_run : nullptr, idx_stride, idx_offset, stream,
+                   k2_floor_plane((const float*)h->inv_qn.p, Bc)));
   }
   return 0;
 }

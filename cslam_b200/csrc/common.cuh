@@ -105,6 +105,46 @@ __device__ __forceinline__ void warp_list_stream(u64* list, int k, u64& thr, con
   }
 }
 
+// Per-warp running top-k.  k == 1: the best key is the register `thr`.  k <= 32: lane j holds the
+// j-th best key in `mine` (sorted descending, 0 = empty).  k > 32: sorted list in shared memory.
+// `floor` (optional): a proven lower bound of the final k-th key; anything below it is dropped even
+// while the list is not full yet (used by the merge steps, where it removes most insertions).
+__device__ __forceinline__ void offer(u64* list, int k, u64 key, bool have, u64& thr, u64& mine,
+                                      int lane, u64 floor = 0ull) {
+  unsigned m = __ballot_sync(kFull, have && key > thr && key >= floor);
+  if (m == 0) return;  // the common case after warm-up
+  if (k == 1) {
+    u64 best = (have && key > thr) ? key : 0ull;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const u64 o = __shfl_xor_sync(kFull, best, off);
+      best = o > best ? o : best;
+    }
+    thr = best;  // best > old thr by construction
+  } else if (k <= 32) {
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const u64 cand = __shfl_sync(kFull, key, src);
+      if (cand > thr) {
+        const int pos = __popc(__ballot_sync(kFull, lane < k && mine > cand));
+        const u64 up = __shfl_up_sync(kFull, mine, 1);
+        if (lane < k) {
+          if (lane > pos) mine = up;
+          else if (lane == pos) mine = cand;
+        }
+        thr = __shfl_sync(kFull, mine, k - 1);
+      }
+    }
+  } else {
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      warp_list_insert(list, k, __shfl_sync(kFull, key, src), thr, lane);
+    }
+  }
+}
+
 // Block-wide exact select: out[r] = the candidate with exactly r larger candidates, for r < k.
 // Keys are unique (they embed the row) except for empties (0), which are skipped.  `out[0..k)` must be
 // zeroed and visible to the block before the call; all threads of the block call it.  O(M^2 / threads)

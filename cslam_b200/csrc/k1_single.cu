@@ -74,46 +74,6 @@ __device__ __forceinline__ float cos_fast(float dot, float nn, float inv_qn) {
   return dot * rsqrtf(fmaxf(nn, kEps * kEps)) * inv_qn;
 }
 
-// Per-warp running top-k.  k == 1: the best key is the register `thr`.  k <= 32: lane j holds the
-// j-th best key in `mine` (sorted descending, 0 = empty).  k > 32: sorted list in shared memory.
-// `floor` (optional): a proven lower bound of the final k-th key; anything below it is dropped even
-// while the list is not full yet (used by the merge steps, where it removes most insertions).
-__device__ __forceinline__ void offer(u64* list, int k, u64 key, bool have, u64& thr, u64& mine,
-                                      int lane, u64 floor = 0ull) {
-  unsigned m = __ballot_sync(kFull, have && key > thr && key >= floor);
-  if (m == 0) return;  // the common case after warm-up
-  if (k == 1) {
-    u64 best = (have && key > thr) ? key : 0ull;
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-      const u64 o = __shfl_xor_sync(kFull, best, off);
-      best = o > best ? o : best;
-    }
-    thr = best;  // best > old thr by construction
-  } else if (k <= 32) {
-    while (m) {
-      const int src = __ffs(m) - 1;
-      m &= m - 1;
-      const u64 cand = __shfl_sync(kFull, key, src);
-      if (cand > thr) {
-        const int pos = __popc(__ballot_sync(kFull, lane < k && mine > cand));
-        const u64 up = __shfl_up_sync(kFull, mine, 1);
-        if (lane < k) {
-          if (lane > pos) mine = up;
-          else if (lane == pos) mine = cand;
-        }
-        thr = __shfl_sync(kFull, mine, k - 1);
-      }
-    }
-  } else {
-    while (m) {
-      const int src = __ffs(m) - 1;
-      m &= m - 1;
-      warp_list_insert(list, k, __shfl_sync(kFull, key, src), thr, lane);
-    }
-  }
-}
-
 // NQ > 0: the query lives in registers (NQ float4 per lane), rows are whole inside one tile.
 // NQ == 0: rows longer than a stage; the query is staged in shared memory and a row is accumulated
 //          across column chunks.

@@ -418,7 +418,8 @@ int k2s_grid(long long n, int num_sms) {
 cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_planes, float* inv_qn,
                        cudaStream_t stream) {
   // inv_qn buffer layout: [inv_qn (B)][q_mean (B)][shared threshold (B, u32)] — callers size it 3x
-  k2_prepare_kernel<<<B, 128, 0, stream>>>(q, dim, q_ld, q_planes, q_planes + (size_t)B * q_ld, inv_qn,
+  const int threads = dim >= 2048 ? 512 : (dim >= 512 ? 256 : 128);  // three latency-bound passes per block
+  k2_prepare_kernel<<<B, threads, 0, stream>>>(q, dim, q_ld, q_planes, q_planes + (size_t)B * q_ld, inv_qn,
                                           inv_qn + B);
   count_launch();
   return cudaGetLastError();

@@ -661,6 +661,10 @@ int k2_parts(long long n, int B, int num_sms) {
   }
 }
 
+const unsigned* k2_floor_plane(const float* inv_qn, int B) {
+  return q_route(B) == 0 ? reinterpret_cast<const unsigned*>(inv_qn + 2 * B) : nullptr;
+}
+
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
   switch (q_route(a.B)) {
     case 0: return q_env_bk() == 16 ? qlaunch<16>(a, num_sms, stream, err) : qlaunch<32>(a, num_sms, stream, err);

@@ -49,7 +49,10 @@ cudaError_t sort_select(const float* all_sims, long long n, int k, void* temp, s
 // keys laid out [parts][B][k_in]; writes B x k_out (k_out <= k_in is fine).
 cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_out, u64* out_keys,
                      long long* out_idx, float* out_sim, long long idx_stride,
-                     long long idx_offset, cudaStream_t stream);
+                     long long idx_offset, cudaStream_t stream, const unsigned* floor_ord = nullptr);
+// the per-query shared threshold plane the query-major batched kernel leaves behind ([B] ordered uints inside
+// the inv_qn buffer), or null when the batch was served by the row-major kernel
+const unsigned* k2_floor_plane(const float* inv_qn, int B);
 
 // ---- K2: batched tcgen05 3xTF32 GEMM + fused per-query top-k (k2_batched.cu) --------------------
 static constexpr int kK2MaxBatch = 256;  // queries per pass (UMMA N)
