@@ -177,10 +177,10 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
   int variant = h->variant;
   if (variant == 0) {
     if (k_run > kK1MaxK) variant = 3;
-    else if (B >= 2 && k2_supported((int)(B > kK2MaxBatch ? kK2MaxBatch : B), k_run)) variant = 2;
+    else if (B >= 2 && k2_supported((int)(B > kK2MaxBatch ? kK2MaxBatch : B), k_run, h->dim)) variant = 2;
     else variant = 1;
   }
-  if (variant == 2 && !k2_supported((int)(B > kK2MaxBatch ? kK2MaxBatch : B), k_run))
+  if (variant == 2 && !k2_supported((int)(B > kK2MaxBatch ? kK2MaxBatch : B), k_run, h->dim))
     return fail(h, CSLAM_NNS_EINVAL, "k does not fit the batched kernel's fused select");
   if (variant == 1 && k_run > kK1MaxK)
     return fail(h, CSLAM_NNS_EINVAL, "k exceeds the fused single-query select (128)");
@@ -251,7 +251,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
   if (!d.tensorMapEncodeTiled) return fail(h, CSLAM_NNS_ECUDA, "cuTensorMapEncodeTiled unavailable");
   for (long long b0 = 0; b0 < B; b0 += kK2MaxBatch) {
     const int Bc = (int)((B - b0) > kK2MaxBatch ? kK2MaxBatch : (B - b0));
-    const int grid = k2_parts(h->n, Bc, h->num_sms);
+    const int grid = k2_parts(h->n, Bc, h->dim, h->num_sms);
     if (!h->q_lo.ensure((size_t)2 * Bc * q_ld * 4) || !h->inv_qn.ensure((size_t)3 * Bc * 4) ||
         !h->part_keys.ensure((size_t)grid * Bc * k_run * 8))
       return fail(h, CSLAM_NNS_ENOMEM, "batched scratch");
@@ -280,7 +280,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
     CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run,
                    o_keys ? o_keys + b0 * k_run : nullptr, o_idx ? o_idx + b0 * k_run : nullptr,
                    o_sim ? o_sim + b0 * k_run : nullptr, idx_stride, idx_offset, stream,
-                   k2_floor_plane((const float*)h->inv_qn.p, Bc)));
+                   k2_floor_plane((const float*)h->inv_qn.p, Bc, h->dim)));
   }
   return 0;
 }

@@ -31,6 +31,7 @@
 // MMAs of tile i+1.
 #include <cuda.h>
 
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -40,9 +41,12 @@ namespace {
 constexpr int BM = 128;          // database rows per tile (UMMA M)
 constexpr int BK = 32;           // floats per K block = 128 bytes = one swizzle row
 constexpr int kEpiThreads = 128, kConvThreads = 128;
-constexpr int kThreads = 320;
+constexpr int kThreads = 352;    // 4 epilogue + 4 converter warps, X producer, MMA issuer, Q producer
 constexpr int kQueueCap = 256;   // per epilogue warp and 8-query chunk: 2 queries x 128 rows
 constexpr int kTmemCols = 512;
+constexpr int kMaxXSlots = 8;    // raw database tiles in flight (shared memory)
+constexpr int kMaxASlots = 4;    // split tiles waiting for the tensor core (tensor memory) + their query tiles
+constexpr int kASlotCols = 2 * BK;  // x_hi (32 columns) then x_lo (32 columns)
 
 struct K2Dev {
   long long n;
@@ -50,8 +54,10 @@ struct K2Dev {
   int B;        // real queries
   int BN;       // padded to a multiple of 16 (UMMA N)
   int k;
-  int stages;
+  int xslots;   // raw-tile ring depth
+  int aslots;   // operand ring depth
   int kblocks;  // ceil(dim / 32)
+  int dbg;      // CSLAM_NNS_K2_DBG experiments (wrong results): 1 no conversion, 2 one product, 4 no scan
   uint32_t idesc;
   const float* inv_qn;
   const float* q_mean;
@@ -60,18 +66,17 @@ struct K2Dev {
 
 // shared-memory carve-up (offsets from a 1024-byte aligned base)
 struct Smem {
-  uint32_t stage_bytes, a_lo_off, b_hi_off, b_lo_off;  // within a stage (a_raw at 0)
+  uint32_t x_bytes, q_bytes;  // one raw-tile slot; one query slot (q_hi plane then q_lo plane)
+  uint32_t q_off;             // start of the query ring (the raw-tile ring starts at 0)
   uint32_t lists_off, thr_off, invq_off, qmean_off, queue_off, qcnt_off, norm_off, bars_off, tmem_off, total;
 };
 
-__host__ __device__ inline Smem carve(int BN, int B, int k, int stages) {
+__host__ __device__ inline Smem carve(int BN, int B, int k, int xslots, int aslots) {
   Smem s;
-  s.a_lo_off = BM * BK * 4;
-  s.b_hi_off = 2 * BM * BK * 4;
-  s.b_lo_off = s.b_hi_off + (uint32_t)BN * BK * 4;
-  s.stage_bytes = s.b_lo_off + (uint32_t)BN * BK * 4;  // multiple of 1024 because BN % 16 == 0 -> BN*128 % 1024? see below
-  s.stage_bytes = (s.stage_bytes + 1023u) & ~1023u;
-  uint32_t o = s.stage_bytes * (uint32_t)stages;
+  s.x_bytes = BM * BK * 4;
+  s.q_bytes = 2u * (uint32_t)BN * BK * 4;  // BN % 16 == 0 -> each plane is a multiple of 2048 bytes
+  uint32_t o = s.x_bytes * (uint32_t)xslots;
+  s.q_off = o;      o += s.q_bytes * (uint32_t)aslots;
   s.lists_off = o;  o += (uint32_t)B * k * 8;
   s.thr_off = o;    o += (uint32_t)BN * 4;
   s.invq_off = o;   o += (uint32_t)BN * 4;
@@ -81,7 +86,7 @@ __host__ __device__ inline Smem carve(int BN, int B, int k, int stages) {
   s.qcnt_off = o;   o += 16;
   s.norm_off = o;   o += 4u * BM * 4;  // [2][BM] |x|^2 then [2][BM] sum(x)
   o = (o + 7u) & ~7u;
-  s.bars_off = o;   o += (3u * 16 + 6) * 8;   // full/conv/empty (<=16 stages) + 3 x 2 accumulator barriers
+  s.bars_off = o;   o += 40u * 8;      // see the barrier table in the kernel
   s.tmem_off = o;   o += 16;
   s.total = o;
   return s;
@@ -103,15 +108,15 @@ __device__ __forceinline__ float tf32_rna(float x) {
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_qhi,
-          const __grid_constant__ CUtensorMap map_qlo, const K2Dev p) {
+k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_q,
+          const K2Dev p) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024 the swizzle needs
   unsigned char* smem = reinterpret_cast<unsigned char*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const Smem L = carve(p.BN, p.B, p.k, p.stages);
+  const Smem L = carve(p.BN, p.B, p.k, p.xslots, p.aslots);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int S = p.stages;
+  const int SX = p.xslots, SA = p.aslots;
 
   u64* lists = reinterpret_cast<u64*>(smem + L.lists_off);
   uint32_t* thr32 = reinterpret_cast<uint32_t*>(smem + L.thr_off);
@@ -122,12 +127,14 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   float* norms = reinterpret_cast<float*>(smem + L.norm_off);
   float* sums = norms + 2 * BM;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars_off);
-  uint64_t* full_bar = bars;             // [S]  TMA landed
-  uint64_t* conv_bar = bars + 16;        // [S]  x_hi / x_lo written
-  uint64_t* empty_bar = bars + 32;       // [S]  MMAs that read the stage are done
-  uint64_t* acc_full = bars + 48;        // [2]  accumulator complete
-  uint64_t* acc_empty = bars + 50;       // [2]  accumulator drained by the epilogue
-  uint64_t* norm_bar = bars + 52;        // [2]  row norms of the tile are in smem
+  uint64_t* x_full = bars;               // [SX] raw tile landed (TMA)                   X producer -> converter
+  uint64_t* x_empty = bars + 8;          // [SX] raw tile is in registers                converter  -> X producer
+  uint64_t* q_full = bars + 16;          // [SA] query planes of the K block landed      Q producer -> MMA
+  uint64_t* a_full = bars + 20;          // [SA] x_hi / x_lo are in tensor memory        converter  -> MMA
+  uint64_t* a_empty = bars + 24;         // [SA] the MMAs reading the slot are done      MMA -> converter, Q producer
+  uint64_t* acc_full = bars + 28;        // [2]  accumulator complete
+  uint64_t* acc_empty = bars + 30;       // [2]  accumulator drained by the epilogue
+  uint64_t* norm_bar = bars + 32;        // [2]  row norms of the tile are in smem
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
 
   // ---- one-time setup -----------------------------------------------------------------------------
@@ -139,10 +146,14 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   }
   if (tid < 4) qcnt[tid] = 0;
   if (tid == 0) {
-    for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&conv_bar[s], kConvThreads);
-      mbar_init(&empty_bar[s], 1);
+    for (int s = 0; s < SX; ++s) {
+      mbar_init(&x_full[s], 1);
+      mbar_init(&x_empty[s], kConvThreads / 32);
+    }
+    for (int s = 0; s < SA; ++s) {
+      mbar_init(&q_full[s], 1);
+      mbar_init(&a_full[s], kConvThreads);
+      mbar_init(&a_empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
@@ -156,97 +167,136 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // tensor-memory map: columns [0, 2*BN) two accumulators, then SA operand slots of 64 columns
+  const uint32_t a_col0 = (uint32_t)(2 * p.BN);
 
   const long long tiles = (p.n + BM - 1) / BM;
   const long long my_tiles =
       (long long)blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
   if (warp == 8) {
-    // ===== TMA producer =============================================================================
+    // ===== X producer: raw database tiles, as deep a ring as shared memory allows ====================
     if (lane == 0) {
       tma_prefetch_desc(&map_a);
-      tma_prefetch_desc(&map_qhi);
-      tma_prefetch_desc(&map_qlo);
-      const uint32_t tx = (uint32_t)(BM * BK * 4 + 2 * p.BN * BK * 4);
       int s = 0;
-      uint32_t ph = 0;  // ring position / wrap parity advanced incrementally: a 64-bit div/mod per stage in
+      uint32_t ph = 0;  // ring position / wrap parity advanced incrementally: a 64-bit div/mod per slot in
                         // a single-thread role costs ~500 clk of dependent latency
       for (long long t = 0; t < my_tiles; ++t) {
         const int row0 = (int)((blockIdx.x + t * gridDim.x) * BM);
-        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
-          mbar_wait(&empty_bar[s], ph ^ 1);
-          unsigned char* st = smem + (size_t)s * L.stage_bytes;
-          mbar_expect_tx(&full_bar[s], tx);
-          tma_load_2d(st, &map_a, kb * BK, row0, &full_bar[s]);
-          tma_load_2d(st + L.b_hi_off, &map_qhi, kb * BK, 0, &full_bar[s]);
-          tma_load_2d(st + L.b_lo_off, &map_qlo, kb * BK, 0, &full_bar[s]);
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == SX ? 0 : s + 1), ph ^= (s == 0)) {
+          mbar_wait(&x_empty[s], ph ^ 1);
+          mbar_expect_tx(&x_full[s], L.x_bytes);
+          tma_load_2d_hint(smem + (size_t)s * L.x_bytes, &map_a, kb * BK, row0, &x_full[s], kEvictFirst);
+        }
+      }
+    }
+  } else if (warp == 10) {
+    // ===== Q producer: both query planes of the K block as ONE 3-D box (they stay L2 resident) =======
+    if (lane == 0) {
+      tma_prefetch_desc(&map_q);
+      int s = 0;
+      uint32_t ph = 0;
+      for (long long t = 0; t < my_tiles; ++t) {
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == SA ? 0 : s + 1), ph ^= (s == 0)) {
+          mbar_wait(&a_empty[s], ph ^ 1);
+          mbar_expect_tx(&q_full[s], L.q_bytes);
+          tma_load_3d_hint(smem + L.q_off + (size_t)s * L.q_bytes, &map_q, kb * BK, 0, 0, &q_full[s],
+                           kEvictLast);
         }
       }
     }
   } else if (warp == 9) {
-    // ===== MMA issuer ===============================================================================
-    if (lane == 0) {
+    // ===== MMA issuer: A = split database tile in TENSOR MEMORY, B = query planes in shared memory ====
+    // The WHOLE warp runs the loop and one elected lane issues: inside an `if (lane == 0)` region ptxas
+    // treats every operand as divergent and wraps each tcgen05.mma in an ELECT / R2UR.BROADCAST loop
+    // (~90 clk per instruction, measured: 12 small MMAs per K block cost more than the HBM time of the block).
+    {
       int s = 0;
       uint32_t ph = 0;
+      const uint32_t lo_plane = (uint32_t)p.BN * BK * 4;
+      const uint32_t q_ring = smem_u32(smem + L.q_off);
       for (long long t = 0; t < my_tiles; ++t) {
         const int a = (int)(t & 1);
         mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(a * p.BN);
-        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
-          mbar_wait(&full_bar[s], ph);
-          mbar_wait(&conv_bar[s], ph);
+        for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == SA ? 0 : s + 1), ph ^= (s == 0)) {
+          mbar_wait(&q_full[s], ph);
+          mbar_wait(&a_full[s], ph);
           tc_fence_after();
-          const uint32_t st = smem_u32(smem + (size_t)s * L.stage_bytes);
+          const uint32_t qs = q_ring + (uint32_t)s * L.q_bytes;
+          const uint32_t at = tmem_base + a_col0 + (uint32_t)(s * kASlotCols);
+          const uint64_t b_hi = make_desc(qs), b_lo = make_desc(qs + lo_plane);
+          const uint32_t first = kb != 0 ? 1u : 0u;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < BK / 8; ++ks) {
-            const uint64_t a_hi = make_desc(st + ks * 32);
-            const uint64_t a_lo = make_desc(st + L.a_lo_off + ks * 32);
-            const uint64_t b_hi = make_desc(st + L.b_hi_off + ks * 32);
-            const uint64_t b_lo = make_desc(st + L.b_lo_off + ks * 32);
-            umma_tf32_ss(d_tmem, a_lo, b_hi, p.idesc, (kb | ks) != 0 ? 1u : 0u);
-            umma_tf32_ss(d_tmem, a_hi, b_lo, p.idesc, 1u);
-            umma_tf32_ss(d_tmem, a_hi, b_hi, p.idesc, 1u);
+            for (int ks = 0; ks < BK / 8; ++ks) {
+              // advancing 32 bytes along K inside the swizzle atom = +2 in the descriptor's address field
+              umma_tf32_ts(d_tmem, at + BK + ks * 8, b_hi + 2 * ks, p.idesc, ks ? 1u : first);  // x_lo * q_hi
+              if (p.dbg & 2) continue;
+              umma_tf32_ts(d_tmem, at + ks * 8, b_lo + 2 * ks, p.idesc, 1u);                      // x_hi * q_lo
+              umma_tf32_ts(d_tmem, at + ks * 8, b_hi + 2 * ks, p.idesc, 1u);                      // x_hi * q_hi
+            }
+            umma_commit(&a_empty[s]);  // implies tcgen05.fence::before_thread_sync
           }
-          umma_commit(&empty_bar[s]);  // implies tcgen05.fence::before_thread_sync
+          __syncwarp();
         }
-        umma_commit(&acc_full[a]);
+        if (elect_one()) umma_commit(&acc_full[a]);
+        __syncwarp();
       }
     }
-  } else if (warp >= 4) {
-    // ===== converter: x -> (x_hi in place, x_lo), row norms ==========================================
-    const int r = tid - 4 * 32;  // tile row owned by this thread
-    int s = 0;
-    uint32_t ph = 0;
+  } else if (warp >= 4 && warp < 8) {
+    // ===== converter: raw tile (smem) -> x_hi, x_lo (tensor memory), row norms ========================
+    // Thread r owns tile row r == TMEM lane r (warp w may only address lanes 32*(w%4)..+31, and 4 % 4 == 0).
+    // The split tiles never touch shared memory: that removes the two 16 KB stores and the three 16 KB
+    // operand fetches per K block that kept the shared-memory pipe ~90% busy (profiles/r1_k2rows_*).
+    const int r = tid - 4 * 32;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    int sx = 0, sa = 0;
+    uint32_t phx = 0, pha = 0;
     for (long long t = 0; t < my_tiles; ++t) {
       const int a = (int)(t & 1);
-      float nn = 0.f, sx = 0.f;
-      for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
-        mbar_wait(&full_bar[s], ph);
-        unsigned char* st = smem + (size_t)s * L.stage_bytes;
-        float4* raw = reinterpret_cast<float4*>(st + (size_t)r * 128);
-        float4* lo = reinterpret_cast<float4*>(st + L.a_lo_off + (size_t)r * 128);
+      float nn = 0.f, sum = 0.f;
+      for (int kb = 0; kb < p.kblocks; ++kb) {
+        uint32_t hi[BK], lo[BK];
+        mbar_wait(&x_full[sx], phx);
+        if (!(p.dbg & 1)) {
+          const float4* raw = reinterpret_cast<const float4*>(smem + (size_t)sx * L.x_bytes + (size_t)r * 128);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int c = (i + r) & 7;  // rotate the 16-byte chunk order: conflict-free across the warp
-          const float4 x = raw[c];
-          float4 h, l;
-          h.x = tf32_hi(x.x); h.y = tf32_hi(x.y); h.z = tf32_hi(x.z); h.w = tf32_hi(x.w);
-          l.x = tf32_rna(x.x - h.x); l.y = tf32_rna(x.y - h.y);
-          l.z = tf32_rna(x.z - h.z); l.w = tf32_rna(x.w - h.w);
-          nn = fmaf(x.x, x.x, nn); nn = fmaf(x.y, x.y, nn);
-          nn = fmaf(x.z, x.z, nn); nn = fmaf(x.w, x.w, nn);
-          sx += (x.x + x.y) + (x.z + x.w);
-          raw[c] = h;
-          lo[c] = l;
+          for (int j = 0; j < 8; ++j) {
+            // 128-byte swizzle: logical 16-byte chunk j of row r sits at chunk j ^ (r & 7); a quarter-warp
+            // therefore reads 8 distinct bank groups
+            const float4 x = raw[j ^ (r & 7)];
+            const float h0 = tf32_hi(x.x), h1 = tf32_hi(x.y), h2 = tf32_hi(x.z), h3 = tf32_hi(x.w);
+            hi[4 * j + 0] = __float_as_uint(h0); hi[4 * j + 1] = __float_as_uint(h1);
+            hi[4 * j + 2] = __float_as_uint(h2); hi[4 * j + 3] = __float_as_uint(h3);
+            lo[4 * j + 0] = __float_as_uint(tf32_rna(x.x - h0)); lo[4 * j + 1] = __float_as_uint(tf32_rna(x.y - h1));
+            lo[4 * j + 2] = __float_as_uint(tf32_rna(x.z - h2)); lo[4 * j + 3] = __float_as_uint(tf32_rna(x.w - h3));
+            nn = fmaf(x.x, x.x, nn); nn = fmaf(x.y, x.y, nn);
+            nn = fmaf(x.z, x.z, nn); nn = fmaf(x.w, x.w, nn);
+            sum += (x.x + x.y) + (x.z + x.w);
+          }
         }
-        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
-        mbar_arrive(&conv_bar[s]);
+        // the raw slot is in registers: hand it back to the producer before waiting for an operand slot
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&x_empty[sx]);
+        mbar_wait(&a_empty[sa], pha ^ 1);
+        tc_fence_after();
+        if (!(p.dbg & 1)) {
+          const uint32_t at = tmem_base + lane_base + a_col0 + (uint32_t)(sa * kASlotCols);
+          tmem_st_32x32b_x32(at, hi);
+          tmem_st_32x32b_x32(at + BK, lo);
+          tmem_st_wait();
+        }
+        tc_fence_before();
+        mbar_arrive(&a_full[sa]);
+        sx = sx + 1 == SX ? 0 : sx + 1; phx ^= (sx == 0);
+        sa = sa + 1 == SA ? 0 : sa + 1; pha ^= (sa == 0);
       }
       // the epilogue of tile t-2 must be done with norms[a] before it is overwritten
       mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
       norms[a * BM + r] = nn;
-      sums[a * BM + r] = sx;
+      sums[a * BM + r] = sum;
       mbar_arrive(&norm_bar[a]);
     }
   } else {
@@ -265,7 +315,7 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       // 1 / max(|x|, eps)  ==  rsqrt(max(|x|^2, eps^2))
       const float inv_nx = rsqrtf(fmaxf(norms[a * BM + r], kEps * kEps));
       const float sum_x = sums[a * BM + r];
-      for (int c0 = 0; c0 < p.BN; c0 += 8) {
+      for (int c0 = 0; c0 < ((p.dbg & 4) ? 0 : p.BN); c0 += 8) {
         uint32_t v[8];
         tmem_ld_32x32b_x8(tmem_base + lane_base + (uint32_t)(a * p.BN + c0), v);
         tmem_ld_wait();
@@ -392,21 +442,48 @@ bool encode_map(void* fn, CUtensorMap* m, const float* base, long long rows, int
                                              promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// both query planes as one 3-D map {dim, B, plane}; rows B..BN-1 of the box are out of bounds -> zero filled
+bool encode_q_map(void* fn, CUtensorMap* m, const float* planes, int B, int dim, int q_ld, int box_rows) {
+  const cuuint64_t gdim[3] = {(cuuint64_t)dim, (cuuint64_t)B, 2};
+  const cuuint64_t gstr[2] = {(cuuint64_t)q_ld * 4, (cuuint64_t)B * q_ld * 4};
+  const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 2};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return reinterpret_cast<EncodeTiledFn>(fn)(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                                             const_cast<float*>(planes), gdim, gstr, box, estr,
+                                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 constexpr size_t kSmemCap = 227 * 1024;
 
 int pad_batch(int B) { return (B + 15) / 16 * 16; }
 
-int pick_stages(int B, int k) {
+// ring depths: as many operand slots as tensor memory holds next to the two accumulators (<= 4), then as
+// many raw-tile slots as the remaining shared memory holds (<= 8, >= 3)
+bool pick_slots(int B, int k, int* xslots, int* aslots) {
   const int BN = pad_batch(B);
-  for (int s = 8; s >= 2; --s)
-    if ((size_t)carve(BN, B, k, s).total + 1024 <= kSmemCap) return s;
-  return 0;
+  int amax = (kTmemCols - 2 * BN) / kASlotCols;
+  if (amax > kMaxASlots) amax = kMaxASlots;
+  for (int sa = amax; sa >= 2; --sa) {
+    const size_t fixed = (size_t)carve(BN, B, k, 0, sa).total + 1024;
+    if (fixed >= kSmemCap) continue;
+    int sx = (int)((kSmemCap - fixed) / (BM * BK * 4));
+    if (sx > kMaxXSlots) sx = kMaxXSlots;
+    if (sx >= 3) {
+      *xslots = sx;
+      *aslots = sa;
+      return true;
+    }
+  }
+  return false;
 }
 
 }  // namespace
 
 bool k2s_supported(int B, int k) {
-  return B >= 1 && B <= kK2MaxBatch && k >= 1 && k <= 32 && pick_stages(B, k) >= 2;
+  int sx, sa;
+  return B >= 1 && B <= kK2MaxBatch && k >= 1 && k <= 32 && pick_slots(B, k, &sx, &sa);
 }
 
 int k2s_grid(long long n, int num_sms) {
@@ -432,7 +509,14 @@ cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const 
   p.B = a.B;
   p.BN = pad_batch(a.B);
   p.k = a.k;
-  p.stages = pick_stages(a.B, a.k);
+  if (!pick_slots(a.B, a.k, &p.xslots, &p.aslots)) {
+    if (err) *err = "k2: batch * k does not fit shared memory";
+    return cudaErrorInvalidConfiguration;
+  }
+  static const int env_stages = getenv("CSLAM_NNS_K2_STAGES") ? atoi(getenv("CSLAM_NNS_K2_STAGES")) : 0;
+  static const int env_dbg = getenv("CSLAM_NNS_K2_DBG") ? atoi(getenv("CSLAM_NNS_K2_DBG")) : 0;
+  if (env_stages >= 2 && env_stages < p.xslots) p.xslots = env_stages;
+  p.dbg = env_dbg;
   p.kblocks = (a.dim + BK - 1) / BK;
   p.inv_qn = a.inv_qn;
   p.q_mean = a.inv_qn + a.B;
@@ -440,20 +524,19 @@ cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const 
   // kind::tf32, fp32 accumulate, both operands K-major: c_format=F32(1)<<4, a/b_format=TF32(2)<<7/<<10,
   // N>>3 at bit 17, M>>4 at bit 24
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-  if (p.stages < 2) {
-    if (err) *err = "k2: batch * k does not fit shared memory";
-    return cudaErrorInvalidConfiguration;
-  }
-  CUtensorMap ma, mh, ml;
-  const float* q_hi = a.q_lo;  // planes written by k2_prepare
-  const float* q_lo = a.q_lo + (size_t)a.B * a.q_ld;
-  if (!encode_map(a.encode_fn, &ma, a.db, a.n, a.dim, a.ld, BM, CU_TENSOR_MAP_L2_PROMOTION_L2_128B) ||
-      !encode_map(a.encode_fn, &mh, q_hi, a.B, a.dim, a.q_ld, p.BN, CU_TENSOR_MAP_L2_PROMOTION_L2_256B) ||
-      !encode_map(a.encode_fn, &ml, q_lo, a.B, a.dim, a.q_ld, p.BN, CU_TENSOR_MAP_L2_PROMOTION_L2_256B)) {
+  CUtensorMap ma, mq;
+  // a.q_lo holds the planes written by k2_prepare: [q_hi (B x q_ld)][q_lo (B x q_ld)]
+  static const int env_promo = getenv("CSLAM_NNS_K2_PROMO") ? atoi(getenv("CSLAM_NNS_K2_PROMO")) : 128;
+  const CUtensorMapL2promotion promo = env_promo == 256  ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+                                       : env_promo == 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                       : env_promo == 0  ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+                                                         : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+  if (!encode_map(a.encode_fn, &ma, a.db, a.n, a.dim, a.ld, BM, promo) ||
+      !encode_q_map(a.encode_fn, &mq, a.q_lo, a.B, a.dim, a.q_ld, p.BN)) {
     if (err) *err = "k2: cuTensorMapEncodeTiled failed";
     return cudaErrorInvalidValue;
   }
-  const size_t smem = carve(p.BN, p.B, p.k, p.stages).total + 1024;
+  const size_t smem = carve(p.BN, p.B, p.k, p.xslots, p.aslots).total + 1024;
   static bool attr_set[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -463,7 +546,7 @@ cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const 
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const int grid = k2s_grid(a.n, num_sms);
-  k2_kernel<<<grid, kThreads, smem, stream>>>(ma, mh, ml, p);
+  k2_kernel<<<grid, kThreads, smem, stream>>>(ma, mq, p);
   count_launch();
   return cudaGetLastError();
 }

@@ -356,7 +356,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             nn = fmaf(x[i].x, x[i].x, nn); nn = fmaf(x[i].y, x[i].y, nn);
             nn = fmaf(x[i].z, x[i].z, nn); nn = fmaf(x[i].w, x[i].w, nn);
             sx += (x[i].x + x[i].y) + (x[i].z + x[i].w);
-            raw[c] = h;
+            if (!(p.dbg & 8)) raw[c] = h;
             lo[c] = l;
           }
           fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
@@ -634,39 +634,43 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
 // queries whatever B is), 2 = row-major one-CTA kernel (k2_batched.cu: MMA N = B padded to 16, cheaper for
 // small batches).  Measured crossover on B200 (2M x 256 and 400k x 4096): between 64 and 128 queries.
 // CSLAM_NNS_K2_FORCE=qm|rows overrides (development).
-int q_route(int B) {
+// Which kernel serves a batch.  Measured on B200 (2M x 256 and 400k x 4096, k = 10): the row-major kernel's
+// epilogue costs ~11 ns per 1000 rows per query whatever the dimension, the query-major pair kernel runs at
+// the tensor-pipe time of 256 queries (~0.5 ns per 1000 rows per float of dimension) whatever the batch, so
+// query-major wins once B * 256 > 45 * dim (B > 45 at dim 256, B > 90 at dim 512, never below 97 from 1024).
+int q_route(int B, int dim) {
   static int forced = -2;
   if (forced == -2) {
     const char* v = getenv("CSLAM_NNS_K2_FORCE");
     forced = !v ? -1 : !strcmp(v, "qm") ? 0 : (!strcmp(v, "rows") || !strcmp(v, "legacy")) ? 2 : -1;
   }
   if (forced >= 0) return forced;
-  return B > 96 ? 0 : 2;
+  return (B > 96 || (long long)B * 256 > 45LL * dim) ? 0 : 2;
 }
 
 }  // namespace
 
-bool k2_supported(int B, int k) {
+bool k2_supported(int B, int k, int dim) {
   if (B < 1 || B > kK2MaxBatch || k < 1 || k > 32) return false;
-  switch (q_route(B)) {
+  switch (q_route(B, dim)) {
     case 0: return (q_env_bk() == 16 ? qpick_stages<16>(k) : qpick_stages<32>(k)) >= 2;
     default: return k2s_supported(B, k);
   }
 }
 
-int k2_parts(long long n, int B, int num_sms) {
-  switch (q_route(B)) {
+int k2_parts(long long n, int B, int dim, int num_sms) {
+  switch (q_route(B, dim)) {
     case 0: return 2 * q_pairs(n, num_sms);
     default: return k2s_grid(n, num_sms);
   }
 }
 
-const unsigned* k2_floor_plane(const float* inv_qn, int B) {
-  return q_route(B) == 0 ? reinterpret_cast<const unsigned*>(inv_qn + 2 * B) : nullptr;
+const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim) {
+  return q_route(B, dim) == 0 ? reinterpret_cast<const unsigned*>(inv_qn + 2 * B) : nullptr;
 }
 
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
-  switch (q_route(a.B)) {
+  switch (q_route(a.B, a.dim)) {
     case 0: return q_env_bk() == 16 ? qlaunch<16>(a, num_sms, stream, err) : qlaunch<32>(a, num_sms, stream, err);
     default: return k2s_launch(a, num_sms, stream, err);
   }

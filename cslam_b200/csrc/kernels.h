@@ -52,7 +52,7 @@ cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_ou
                      long long idx_offset, cudaStream_t stream, const unsigned* floor_ord = nullptr);
 // the per-query shared threshold plane the query-major batched kernel leaves behind ([B] ordered uints inside
 // the inv_qn buffer), or null when the batch was served by the row-major kernel
-const unsigned* k2_floor_plane(const float* inv_qn, int B);
+const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim);
 
 // ---- K2: batched tcgen05 3xTF32 GEMM + fused per-query top-k (k2_batched.cu) --------------------
 static constexpr int kK2MaxBatch = 256;  // queries per pass (UMMA N)
@@ -71,9 +71,9 @@ struct K2Args {
   u64* part_keys;      // [grid][B][k] scratch
   void* encode_fn;     // cuTensorMapEncodeTiled entry point
 };
-bool k2_supported(int B, int k);
+bool k2_supported(int B, int k, int dim);
 // number of partial key lists [parts][B][k] a launch for batch B writes (sizes part_keys, feeds k4_merge)
-int k2_parts(long long n, int B, int num_sms);
+int k2_parts(long long n, int B, int dim, int num_sms);
 // queries (device, pitch q_ld) -> q_lo, inv_qn
 cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_lo, float* inv_qn,
                        cudaStream_t stream);
