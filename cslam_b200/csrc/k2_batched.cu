@@ -42,7 +42,7 @@ constexpr int BM = 128;          // database rows per tile (UMMA M)
 constexpr int BK = 32;           // floats per K block = 128 bytes = one swizzle row
 constexpr int kEpiThreads = 128, kConvThreads = 128;
 constexpr int kThreads = 352;    // 4 epilogue + 4 converter warps, X producer, MMA issuer, Q producer
-constexpr int kQueueCap = 256;   // per epilogue warp and 8-query chunk: 2 queries x 128 rows
+constexpr int kQueueCap = 512;   // per epilogue warp and 16-query chunk: 4 queries x 128 rows
 constexpr int kTmemCols = 512;
 constexpr int kMaxXSlots = 8;    // raw database tiles in flight (shared memory)
 constexpr int kMaxASlots = 4;    // split tiles waiting for the tensor core (tensor memory) + their query tiles
@@ -57,10 +57,12 @@ struct K2Dev {
   int xslots;   // raw-tile ring depth
   int aslots;   // operand ring depth
   int kblocks;  // ceil(dim / 32)
-  int dbg;      // CSLAM_NNS_K2_DBG experiments (wrong results): 1 no conversion, 2 one product, 4 no scan
+  int dbg;      // CSLAM_NNS_K2_DBG experiments (wrong results): 1 no conversion, 2 one product, 4 no scan,
+                // 64 no grid-wide threshold sharing (results stay right)
   uint32_t idesc;
   const float* inv_qn;
   const float* q_mean;
+  unsigned* gthr;  // [B] grid-wide lower bound of each query's k-th best similarity (ordered uint), 0 = none
   u64* part_keys;  // [grid][B][k]
 };
 
@@ -68,7 +70,7 @@ struct K2Dev {
 struct Smem {
   uint32_t x_bytes, q_bytes;  // one raw-tile slot; one query slot (q_hi plane then q_lo plane)
   uint32_t q_off;             // start of the query ring (the raw-tile ring starts at 0)
-  uint32_t lists_off, thr_off, invq_off, qmean_off, queue_off, qcnt_off, norm_off, bars_off, tmem_off, total;
+  uint32_t lists_off, qpar_off, queue_off, qcnt_off, norm_off, bars_off, tmem_off, total;
 };
 
 __host__ __device__ inline Smem carve(int BN, int B, int k, int xslots, int aslots) {
@@ -78,10 +80,8 @@ __host__ __device__ inline Smem carve(int BN, int B, int k, int xslots, int aslo
   uint32_t o = s.x_bytes * (uint32_t)xslots;
   s.q_off = o;      o += s.q_bytes * (uint32_t)aslots;
   s.lists_off = o;  o += (uint32_t)B * k * 8;
-  s.thr_off = o;    o += (uint32_t)BN * 4;
-  s.invq_off = o;   o += (uint32_t)BN * 4;
-  s.qmean_off = o;  o += (uint32_t)BN * 4;
-  o = (o + 7u) & ~7u;
+  o = (o + 15u) & ~15u;
+  s.qpar_off = o;   o += (uint32_t)BN * 16;  // per query {mean(q), 1/|q|, threshold (ordered uint), -}
   s.queue_off = o;  o += 4u * kQueueCap * 8;
   s.qcnt_off = o;   o += 16;
   s.norm_off = o;   o += 4u * BM * 4;  // [2][BM] |x|^2 then [2][BM] sum(x)
@@ -111,17 +111,16 @@ __global__ void __launch_bounds__(kThreads, 1)
 k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_q,
           const K2Dev p) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024 the swizzle needs
-  unsigned char* smem = reinterpret_cast<unsigned char*>(
-      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // dynamic shared memory is only guaranteed 16-byte aligned: round up to the 1024 the swizzle needs.  Offset
+  // the array (do NOT round-trip through uintptr_t: that makes every later access a generic LD.E / ST.E /
+  // ATOM.E instead of LDS / STS / ATOMS, which cost the epilogue ~150 clk per similarity)
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const Smem L = carve(p.BN, p.B, p.k, p.xslots, p.aslots);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int SX = p.xslots, SA = p.aslots;
 
   u64* lists = reinterpret_cast<u64*>(smem + L.lists_off);
-  uint32_t* thr32 = reinterpret_cast<uint32_t*>(smem + L.thr_off);
-  float* invq = reinterpret_cast<float*>(smem + L.invq_off);
-  float* qmean = reinterpret_cast<float*>(smem + L.qmean_off);
+  uint4* qpar = reinterpret_cast<uint4*>(smem + L.qpar_off);
   u64* queue = reinterpret_cast<u64*>(smem + L.queue_off);
   int* qcnt = reinterpret_cast<int*>(smem + L.qcnt_off);
   float* norms = reinterpret_cast<float*>(smem + L.norm_off);
@@ -139,11 +138,9 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
 
   // ---- one-time setup -----------------------------------------------------------------------------
   for (int i = tid; i < p.B * p.k; i += kThreads) lists[i] = 0ull;
-  for (int i = tid; i < p.BN; i += kThreads) {
-    thr32[i] = 0u;
-    invq[i] = i < p.B ? p.inv_qn[i] : 0.f;
-    qmean[i] = i < p.B ? p.q_mean[i] : 0.f;
-  }
+  for (int i = tid; i < p.BN; i += kThreads)
+    qpar[i] = make_uint4(__float_as_uint(i < p.B ? p.q_mean[i] : 0.f), __float_as_uint(i < p.B ? p.inv_qn[i] : 0.f),
+                         0u, 0u);
   if (tid < 4) qcnt[tid] = 0;
   if (tid == 0) {
     for (int s = 0; s < SX; ++s) {
@@ -308,56 +305,82 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const int a = (int)(t & 1);
       const uint32_t ph = (uint32_t)((t >> 1) & 1);
       const long long row0 = (blockIdx.x + t * gridDim.x) * (long long)BM;
+      // grid-wide threshold sharing: every full list's k-th best is a proven lower bound of the final k-th
+      // best, so other CTAs may drop anything BELOW it (ties are kept: a lower row index wins a tie).
+      // Thread q refreshes query q once per tile; the load is issued before the waits that hide it.
+      const unsigned g_new = (tid < p.B && !(p.dbg & 64)) ? __ldcg(p.gthr + tid) : 0u;
       mbar_wait(&norm_bar[a], ph);
       mbar_wait(&acc_full[a], ph);
       tc_fence_after();
+      // (racing with the owner warp's update below is benign: both values are valid lower bounds)
+      if (g_new > 1u && g_new - 1u > qpar[tid].z) qpar[tid].z = g_new - 1u;
       const bool row_ok = row0 + r < p.n;
       // 1 / max(|x|, eps)  ==  rsqrt(max(|x|^2, eps^2))
       const float inv_nx = rsqrtf(fmaxf(norms[a * BM + r], kEps * kEps));
       const float sum_x = sums[a * BM + r];
-      for (int c0 = 0; c0 < ((p.dbg & 4) ? 0 : p.BN); c0 += 8) {
-        uint32_t v[8];
-        tmem_ld_32x32b_x8(tmem_base + lane_base + (uint32_t)(a * p.BN + c0), v);
+      for (int c0 = 0; c0 < ((p.dbg & 4) ? 0 : p.BN); c0 += 16) {
+        uint32_t v[16];
+        tmem_ld_32x32b_x16(tmem_base + lane_base + (uint32_t)(a * p.BN + c0), v);
         tmem_ld_wait();
-        if (c0 < p.B) {
+        if (c0 >= p.B) continue;  // padding columns (uniform over the CTA)
+        // branch-free pass over the chunk: the 16 parameter loads are independent and pipeline, survivors
+        // only set a bit.  (Testing and pushing query by query serialises ~3 shared-memory latencies per
+        // similarity on the one epilogue warp of each scheduler.)
+        uint32_t o[16];
+        uint32_t m = 0;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int q = c0 + j;
-            const float s_ = fmaf(qmean[q], sum_x, __uint_as_float(v[j])) * inv_nx * invq[q];
-            const uint32_t o = sim_to_ord(s_);
-            if (row_ok && q < p.B && o > thr32[q]) {
-              const int slot = atomicAdd(&qcnt[q & 3], 1);
-              queue[(size_t)(q & 3) * kQueueCap + slot] = ((u64)o << 32) | ((u64)q << 8) | (u64)r;
+        for (int j = 0; j < 16; ++j) {
+          const uint4 qp = qpar[c0 + j];
+          const float s_ =
+              fmaf(__uint_as_float(qp.x), sum_x, __uint_as_float(v[j])) * inv_nx * __uint_as_float(qp.y);
+          o[j] = sim_to_ord(s_);
+          m |= (o[j] > qp.z ? 1u : 0u) << j;
+        }
+        const int live = p.B - c0;  // real queries in this chunk
+        m &= row_ok ? (live >= 16 ? 0xffffu : (1u << live) - 1u) : 0u;
+        const bool pushed = m != 0;
+        if (pushed) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (m & (1u << j)) {
+              const int slot = atomicAdd(&qcnt[j & 3], 1);  // (c0 + j) & 3 == j & 3
+              queue[(size_t)(j & 3) * kQueueCap + slot] = ((u64)o[j] << 32) | ((u64)(c0 + j) << 8) | (u64)r;
             }
           }
-          named_bar_sync(1, kEpiThreads);
-          // drain: this warp owns the queries with q & 3 == warp, so no two warps touch one list
-          const int cnt = qcnt[warp];
-          for (int e = 0; e < cnt; ++e) {
-            const u64 ent = myq[e];
-            const int q = (int)((ent >> 8) & 0xff);
-            const uint32_t row = (uint32_t)(row0 + (long long)(ent & 0x7f));
-            const u64 key = (ent & 0xffffffff00000000ull) | (u64)(~row);
-            u64* lst = lists + (size_t)q * p.k;
-            u64 mine = lane < p.k ? lst[lane] : 0ull;
-            const u64 last = __shfl_sync(kFull, mine, p.k - 1);
-            if (key > last) {
-              const int pos = __popc(__ballot_sync(kFull, lane < p.k && mine > key));
-              const u64 up = __shfl_up_sync(kFull, mine, 1);
-              if (lane < p.k) {
-                if (lane > pos) mine = up;
-                else if (lane == pos) mine = key;
-                lst[lane] = mine;
-              }
-              const u64 nl = __shfl_sync(kFull, mine, p.k - 1);
-              if (lane == 0 && nl != 0ull) thr32[q] = (uint32_t)(nl >> 32);
+        }
+        // one barrier tells every epilogue thread whether ANY row of the tile survived a threshold in this
+        // chunk; once the lists have warmed up almost none does and the drain (and its second barrier) is skipped
+        if (!named_bar_or(1, kEpiThreads, pushed)) continue;
+        // drain: this warp owns the queries with q & 3 == warp, so no two warps touch one list
+        const int cnt = qcnt[warp];
+        for (int e = 0; e < cnt; ++e) {
+          const u64 ent = myq[e];
+          const int q = (int)((ent >> 8) & 0xff);
+          const uint32_t row = (uint32_t)(row0 + (long long)(ent & 0x7f));
+          const u64 key = (ent & 0xffffffff00000000ull) | (u64)(~row);
+          u64* lst = lists + (size_t)q * p.k;
+          u64 mine = lane < p.k ? lst[lane] : 0ull;
+          const u64 last = __shfl_sync(kFull, mine, p.k - 1);
+          if (key > last) {
+            const int pos = __popc(__ballot_sync(kFull, lane < p.k && mine > key));
+            const u64 up = __shfl_up_sync(kFull, mine, 1);
+            if (lane < p.k) {
+              if (lane > pos) mine = up;
+              else if (lane == pos) mine = key;
+              lst[lane] = mine;
             }
-            __syncwarp();
+            const u64 nl = __shfl_sync(kFull, mine, p.k - 1);
+            if (lane == 0 && nl != 0ull) {
+              const uint32_t ord = (uint32_t)(nl >> 32);
+              if (ord > qpar[q].z) qpar[q].z = ord;
+              if (ord != 0xffffffffu && !(p.dbg & 64)) atomicMax(p.gthr + q, ord);  // NaN is never a bound
+            }
           }
           __syncwarp();
-          if (lane == 0) qcnt[warp] = 0;
-          named_bar_sync(1, kEpiThreads);
         }
+        __syncwarp();
+        if (lane == 0) qcnt[warp] = 0;
+        named_bar_sync(1, kEpiThreads);
       }
       tc_fence_before();
       mbar_arrive(&acc_empty[a]);
@@ -483,7 +506,7 @@ bool pick_slots(int B, int k, int* xslots, int* aslots) {
 
 bool k2s_supported(int B, int k) {
   int sx, sa;
-  return B >= 1 && B <= kK2MaxBatch && k >= 1 && k <= 32 && pick_slots(B, k, &sx, &sa);
+  return B >= 1 && B <= kRowsMaxBatch && k >= 1 && k <= 32 && pick_slots(B, k, &sx, &sa);
 }
 
 int k2s_grid(long long n, int num_sms) {
@@ -521,6 +544,7 @@ cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const 
   p.inv_qn = a.inv_qn;
   p.q_mean = a.inv_qn + a.B;
   p.part_keys = a.part_keys;
+  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn + 2 * a.B));  // zeroed by k2_prepare
   // kind::tf32, fp32 accumulate, both operands K-major: c_format=F32(1)<<4, a/b_format=TF32(2)<<7/<<10,
   // N>>3 at bit 17, M>>4 at bit 24
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);

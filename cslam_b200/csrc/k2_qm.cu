@@ -285,10 +285,13 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     }
   } else if (warp == 5) {
     // ===== MMA issuer (leader CTA only) =============================================================
-    if (rank == 0 && lane == 0) {
+    // The whole warp runs the loop and one elected lane issues: in an `if (lane == 0)` region ptxas wraps
+    // every tcgen05.mma in an ELECT / BRA.U.ANY loop, which costs about as much as the MMA itself.
+    if (rank == 0) {
       long long w0 = 0, w1 = 0, w2 = 0;
       int s = 0;
       uint32_t ph = 0;
+      const uint32_t ring = smem_u32(smem);
       for (long long t = 0; t < my_tiles; ++t) {
         const int a = (int)(t & 1);
         QPROF_WAIT(w2, mbar_wait_cluster(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
@@ -298,26 +301,30 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           QPROF_WAIT(w0, mbar_wait_cluster(&qfull_bar[s], ph));
           QPROF_WAIT(w1, mbar_wait_cluster(&conv_bar[s], ph));
           tc_fence_after();
-          const uint32_t st = smem_u32(smem + (size_t)s * L.stage_bytes);
+          const uint32_t st = ring + (uint32_t)s * L.stage_bytes;
+          const uint64_t x_hi = qdesc<BK>(st), x_lo = qdesc<BK>(st + L.x_lo_off);
+          const uint64_t q_hi = qdesc<BK>(st + L.q_hi_off), q_lo = qdesc<BK>(st + L.q_lo_off);
+          const uint32_t first = kb != 0 ? 1u : 0u;
+          if (elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < BK / 8; ++ks) {
-            const uint64_t x_hi = qdesc<BK>(st + ks * 32);
-            const uint64_t x_lo = qdesc<BK>(st + L.x_lo_off + ks * 32);
-            const uint64_t q_hi = qdesc<BK>(st + L.q_hi_off + ks * 32);
-            const uint64_t q_lo = qdesc<BK>(st + L.q_lo_off + ks * 32);
-            if (!(p.dbg & 2)) {
-              umma_tf32_ss_pair(d_tmem, q_hi, x_lo, p.idesc, (kb | ks) != 0 ? 1u : 0u);
-              umma_tf32_ss_pair(d_tmem, q_lo, x_hi, p.idesc, 1u);
-              umma_tf32_ss_pair(d_tmem, q_hi, x_hi, p.idesc, 1u);
-            } else {
-              umma_tf32_ss_pair(d_tmem, q_hi, x_hi, p.idesc, (kb | ks) != 0 ? 1u : 0u);
+            for (int ks = 0; ks < BK / 8; ++ks) {
+              const uint64_t adv = (uint64_t)(2 * ks);  // 32 bytes along K = +2 in the 16-byte address field
+              if (!(p.dbg & 2)) {
+                umma_tf32_ss_pair(d_tmem, q_hi + adv, x_lo + adv, p.idesc, ks ? 1u : first);
+                umma_tf32_ss_pair(d_tmem, q_lo + adv, x_hi + adv, p.idesc, 1u);
+                umma_tf32_ss_pair(d_tmem, q_hi + adv, x_hi + adv, p.idesc, 1u);
+              } else {
+                umma_tf32_ss_pair(d_tmem, q_hi + adv, x_hi + adv, p.idesc, ks ? 1u : first);
+              }
             }
+            umma_commit_pair(&empty_bar[s]);
           }
-          umma_commit_pair(&empty_bar[s]);
+          __syncwarp();
         }
-        umma_commit_pair(&acc_full[a]);
+        if (elect_one()) umma_commit_pair(&acc_full[a]);
+        __syncwarp();
       }
-      if (p.prof) {
+      if (p.prof && lane == 0) {
         p.prof[blockIdx.x * 16 + 2] = (u64)w0;
         p.prof[blockIdx.x * 16 + 3] = (u64)w1;
         p.prof[blockIdx.x * 16 + 4] = (u64)w2;
@@ -634,18 +641,19 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
 // queries whatever B is), 2 = row-major one-CTA kernel (k2_batched.cu: MMA N = B padded to 16, cheaper for
 // small batches).  Measured crossover on B200 (2M x 256 and 400k x 4096): between 64 and 128 queries.
 // CSLAM_NNS_K2_FORCE=qm|rows overrides (development).
-// Which kernel serves a batch.  Measured on B200 (2M x 256 and 400k x 4096, k = 10): the row-major kernel's
-// epilogue costs ~11 ns per 1000 rows per query whatever the dimension, the query-major pair kernel runs at
-// the tensor-pipe time of 256 queries (~0.5 ns per 1000 rows per float of dimension) whatever the batch, so
-// query-major wins once B * 256 > 45 * dim (B > 45 at dim 256, B > 90 at dim 512, never below 97 from 1024).
+// Which kernel serves a batch.  Measured on B200 (2M x 256 and 400k x 4096, k = 10; profiles/r1_k2rows_*):
+// the row-major kernel runs at max(HBM time, ~0.13 + 0.0053 * B ns per row) whatever the dimension (its
+// epilogue sees every row x query pair), the query-major pair kernel at the tensor-pipe time of 256 queries
+// (~0.002 ns per row per float of dimension) whatever the batch, so query-major wins once B * 256 > 72 * dim
+// (B > 72 at dim 256, never below 97 from dim 384 up).
 int q_route(int B, int dim) {
   static int forced = -2;
   if (forced == -2) {
     const char* v = getenv("CSLAM_NNS_K2_FORCE");
     forced = !v ? -1 : !strcmp(v, "qm") ? 0 : (!strcmp(v, "rows") || !strcmp(v, "legacy")) ? 2 : -1;
   }
-  if (forced >= 0) return forced;
-  return (B > 96 || (long long)B * 256 > 45LL * dim) ? 0 : 2;
+  if (forced == 0 || (forced == 2 && B <= kRowsMaxBatch)) return forced;
+  return (B > 96 || (long long)B * 256 > 72LL * dim) ? 0 : 2;
 }
 
 }  // namespace
@@ -666,7 +674,8 @@ int k2_parts(long long n, int B, int dim, int num_sms) {
 }
 
 const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim) {
-  return q_route(B, dim) == 0 ? reinterpret_cast<const unsigned*>(inv_qn + 2 * B) : nullptr;
+  (void)dim;  // both kernels publish their bounds in the third plane
+  return reinterpret_cast<const unsigned*>(inv_qn + 2 * B);
 }
 
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {

@@ -56,6 +56,9 @@ const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim);
 
 // ---- K2: batched tcgen05 3xTF32 GEMM + fused per-query top-k (k2_batched.cu) --------------------
 static constexpr int kK2MaxBatch = 256;  // queries per pass (UMMA N)
+// row-major kernel: two accumulators (2 * padded batch columns) and >= 2 operand slots (64 columns each)
+// share the 512 columns of tensor memory
+static constexpr int kRowsMaxBatch = 192;
 static constexpr int kK2ListBudget = 2560;  // k * padded batch must not exceed this (smem lists)
 
 struct K2Args {
