@@ -116,6 +116,46 @@ def test_golden_config1_loop_closure_sparse_matching(golden_config1):
     assert len(mism) <= 2, mism[:5]   # only reference-tie cases may differ
 
 
+def test_batched_messages_equal_looped():
+    """a GlobalDescriptors message carries several descriptors; handing them to
+    add_other_robot_global_descriptors (ONE batched search of the local database) must give the same
+    matches and the same candidate edges as the reference's per-descriptor loop
+    (global_descriptor_loop_closure_detection.py:388-404 -> loop_closure_sparse_matching.py:58-76)."""
+    from cslam_b200.loop_closure_sparse_matching import CandidateEdges, LoopClosureSparseMatching
+    GD = namedtuple("GlobalDescriptor", ["keyframe_id", "robot_id", "descriptor"])
+    params = {"robot_id": 0, "max_nb_robots": 3, "frontend.sensor_type": "stereo",
+              "frontend.similarity_threshold": 0.7, "frontend.nb_best_matches": 10,
+              "frontend.intra_loop_min_inbetween_keyframes": 10}
+    local = synth.unit_rows(51, 3000, 128, "randn")
+    remote = synth.queries_for(52, local, 90, "randn", every=2, noise=0.03)
+    msgs = [GD(1000 + i, 1 + (i % 2), remote[i].tolist()) for i in range(len(remote))]
+
+    def run(batched):
+        lcsm = LoopClosureSparseMatching(params, candidate_selector=CandidateEdges(0, 3))
+        for i in range(len(local)):
+            lcsm.add_local_global_descriptor(local[i], i)
+        out = []
+        for c in range(0, len(msgs), 10):   # the reference publishes descriptors in chunks (:192-221)
+            chunk = msgs[c:c + 10]
+            out += lcsm.add_other_robot_global_descriptors(chunk) if batched else \
+                [lcsm.add_other_robot_global_descriptor(m) for m in chunk]
+        return lcsm, out
+
+    la, a = run(False)
+    lb, b = run(True)
+    assert sum(m is not None for m in a) == 45          # exactly the planted revisits pass the threshold
+    for ma, mb in zip(a, b):
+        assert (ma is None) == (mb is None)
+        if ma is not None:
+            assert (ma.robot0_keyframe_id, ma.robot1_id, ma.robot1_keyframe_id) == \
+                (mb.robot0_keyframe_id, mb.robot1_id, mb.robot1_keyframe_id)
+            assert abs(ma.weight - mb.weight) <= 1e-5 * abs(ma.weight) + 1e-6
+    assert sorted(la.candidate_selector.candidate_edges) == sorted(lb.candidate_selector.candidate_edges)
+    for rid in (1, 2):   # the other robots' databases received the same rows in the same order
+        assert la.other_robots_nnsm[rid].n == lb.other_robots_nnsm[rid].n == 45
+        assert la.other_robots_nnsm[rid].items == lb.other_robots_nnsm[rid].items
+
+
 # ---- oracle on seeded inputs ------------------------------------------------------------------------
 
 @pytest.mark.parametrize("n,d,k,dist", [
