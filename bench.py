@@ -174,7 +174,7 @@ def reference_arm(args, rows, dim, batch, k):
 
 def workload_config(args, rows, dim, batch, k):
     return {"workload": WORKLOADS[args.workload][4], "rows": rows, "dim": dim, "batch": batch, "k": k,
-            "sharding": "row-striped over %d rank(s), one all-gather of B*k keys per step" % args.gpus
+            "sharding": "row-striped over %d rank(s), one exchange of B*k keys per rank per step" % args.gpus
             if args.gpus > 1 else "single GPU",
             "l2": "database (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (rows * dim * 4 / 1e9)}
 
@@ -429,7 +429,9 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products, fp32 accumulate)"
             if variant == 2 else "f32", "data": "synthetic",
-            "config": dict(workload_config(args, rows, dim, batch, k), search_variant=variant),
+            "config": dict(workload_config(args, rows, dim, batch, k), search_variant=variant,
+                           **({"exchange": "K5 peer-memory kernel (csrc/k5_exchange.cu)"
+                               if getattr(m, "_xchg", None) is not None else "NCCL all-gather + K4"} if world > 1 else {})),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches)}
     print(json.dumps(line))
     if world > 1:

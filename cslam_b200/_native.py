@@ -52,6 +52,18 @@ SIGNATURES = {
 
 # include/cslam_scancontext.h (ScanContext matcher)
 _f64p = _c.c_void_p
+XCHG_SIGNATURES = {
+    "cslam_nns_xchg_last_error": (_c.c_char_p, [_handle]),
+    "cslam_nns_xchg_create": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.POINTER(_handle)]),
+    "cslam_nns_xchg_destroy": (_c.c_int, [_handle]),
+    "cslam_nns_xchg_export": (_c.c_int, [_handle, _c.c_void_p]),
+    "cslam_nns_xchg_connect": (_c.c_int, [_handle, _c.c_void_p]),
+    "cslam_nns_xchg_connect_local": (_c.c_int, [_handle, _c.POINTER(_handle)]),
+    "cslam_nns_xchg_merge": (_c.c_int, [_handle, _c.c_void_p, _i64, _c.c_int, _c.c_int, _c.c_void_p,
+                                        _c.c_void_p, _c.c_void_p]),
+    "cslam_nns_xchg_status": (_c.c_int, [_handle]),
+}
+
 SC_SIGNATURES = {
     "cslam_sc_last_error": (_c.c_char_p, [_handle]),
     "cslam_sc_create": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _i64, _c.POINTER(_handle)]),
@@ -85,7 +97,7 @@ def load():
             "(or `python -c 'import __graft_entry__ as g; g.build()'`). "
             "cslam_b200 has no CPU or PyTorch fallback.")
     lib = ctypes.CDLL(LIB_PATH)
-    for name, (res, args) in list(SIGNATURES.items()) + list(SC_SIGNATURES.items()):
+    for name, (res, args) in list(SIGNATURES.items()) + list(SC_SIGNATURES.items()) + list(XCHG_SIGNATURES.items()):
         fn = getattr(lib, name)  # AttributeError here == header/library mismatch
         fn.restype = res
         fn.argtypes = args

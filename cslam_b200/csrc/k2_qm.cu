@@ -349,13 +349,16 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           float4 x[kChunks];
 #pragma unroll
           for (int i = 0; i < kChunks; ++i) {
-            // rotate the chunk order so that a quarter-warp touches 8 distinct 16-byte bank groups
-            const int c = BK == 32 ? ((i + r) & 7) : ((i + (r >> 1)) & 3);
+            // LOGICAL 16-byte chunk i of the row sits at physical chunk i ^ (swizzle bits of the row): a
+            // quarter-warp touches 8 distinct bank groups, and |x|^2 / sum(x) are accumulated in column
+            // order whatever the row's position in the tile, so a row's similarity does not depend on how
+            // the database is partitioned (bit-identical results for any shard count)
+            const int c = BK == 32 ? (i ^ (r & 7)) : (i ^ ((r >> 1) & 3));
             x[i] = raw[c];
           }
 #pragma unroll
           for (int i = 0; i < kChunks; ++i) {
-            const int c = BK == 32 ? ((i + r) & 7) : ((i + (r >> 1)) & 3);
+            const int c = BK == 32 ? (i ^ (r & 7)) : (i ^ ((r >> 1) & 3));
             float4 h, l;
             h.x = q_tf32_hi(x[i].x); h.y = q_tf32_hi(x[i].y); h.z = q_tf32_hi(x[i].z); h.w = q_tf32_hi(x[i].w);
             l.x = q_tf32_rna(x[i].x - h.x); l.y = q_tf32_rna(x[i].y - h.y);

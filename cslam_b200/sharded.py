@@ -4,7 +4,13 @@ The reference has no multi-GPU path for the matcher; this is the additive scalin
 BASELINE.json's north_star.  Global row ``i`` lives on rank ``i % world`` as local row ``i // world``
 (striped, so incremental ``add_item`` stays balanced and nothing is ever re-balanced).  A search is
 
-    local top-k on every rank  ->  ONE all_gather of B*k packed 64-bit keys  ->  merge kernel (K4)
+    local top-k on every rank  ->  exchange of B*k packed 64-bit keys per rank  ->  merge
+
+On GPUs the exchange and the merge are ONE kernel (K5, ``csrc/k5_exchange.cu``): every rank stores its keys
+into every rank's exchange buffer over NVLink peer memory (opened once with CUDA IPC), publishes them with
+release stores and merges what it received — no NCCL call on the search path.  The NCCL route (one
+``all_gather_into_tensor`` + merge kernel K4) remains for k > 32 or more than 4096 queries per call, and
+when ``CSLAM_NNS_EXCHANGE=nccl`` is set.
 
 The keys carry the global row index and a total order (similarity desc, row asc), so the merged
 result is bit-identical to a single-GPU search of the concatenated database for any world size.
@@ -12,6 +18,8 @@ result is bit-identical to a single-GPU search of the concatenated database for 
 exercised with gloo in the CPU tests through ``plan_rows`` / ``merge_keys_host``).
 """
 import ctypes
+import os
+import warnings
 
 import numpy as np
 import torch
@@ -52,14 +60,58 @@ def merge_keys_host(keys, k):
 class ShardedNearestNeighborsMatching(object):
     """Same three methods as the reference matcher; every rank calls them with the same arguments."""
 
-    def __init__(self, dim=None, group=None):
+    def __init__(self, dim=None, group=None, exchange=None):
+        """exchange: "peer" (K5 over NVLink peer memory, the default on GPUs) or "nccl" (all-gather + K4);
+        None reads CSLAM_NNS_EXCHANGE."""
         self.group = group
+        self.exchange = exchange or os.environ.get("CSLAM_NNS_EXCHANGE", "peer")
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.local = NearestNeighborsMatching(dim)
         self.n = 0            # global row count
         self.items = dict()   # global row -> item (kept on every rank; tiny)
         self.dim = dim
+        self._xchg = None     # peer-memory exchange (K5), opened lazily on the first device search
+        self._xchg_tried = False
+
+    # -- peer-memory exchange ----------------------------------------------------------------------
+    def _exchange(self, device):
+        """Open the K5 exchange once: allocate this rank's buffers, all_gather the CUDA IPC handles, map
+        the peers.  Collective: every rank takes the same branch (the outcome is agreed by an all_reduce)."""
+        if self._xchg_tried:
+            return self._xchg
+        self._xchg_tried = True
+        if self.world == 1 or self.exchange == "nccl" or device.type != "cuda":
+            return None
+        lib = _native.load()
+        x = ctypes.c_void_p()
+        rc = lib.cslam_nns_xchg_create(device.index, self.world, self.rank, ctypes.byref(x))
+        mine = torch.zeros(128, dtype=torch.uint8)
+        if rc == _native.OK:
+            rc = lib.cslam_nns_xchg_export(x, ctypes.c_void_p(mine.data_ptr()))
+        every = torch.empty((self.world, 128), dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(every, mine.to(device), group=self.group)
+        every = every.cpu().contiguous()
+        if rc == _native.OK:
+            rc = lib.cslam_nns_xchg_connect(x, ctypes.c_void_p(every.data_ptr()))
+        ok = torch.tensor([1 if rc == _native.OK else 0], dtype=torch.int32, device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+        if int(ok.item()) == 1:
+            self._xchg = x
+        else:
+            why = lib.cslam_nns_xchg_last_error(x if x.value else None).decode("utf-8", "replace")
+            warnings.warn("peer-memory exchange unavailable (%s); using the NCCL all-gather route" % why)
+            if x.value:
+                lib.cslam_nns_xchg_destroy(x)
+        return self._xchg
+
+    def __del__(self):
+        try:
+            if self._xchg is not None:
+                _native.load().cslam_nns_xchg_destroy(self._xchg)
+                self._xchg = None
+        except Exception:
+            pass
 
     def add_item(self, vector, item):
         if self.dim is None:
@@ -131,14 +183,23 @@ class ShardedNearestNeighborsMatching(object):
             _native.check(rc, h.h)
             return out_idx, out_sim
         keys = self.search_keys_device(q_dev, k)
+        if out_idx is None:
+            out_idx = torch.empty((B, k), dtype=torch.int64, device=q_dev.device)
+            out_sim = torch.empty((B, k), dtype=torch.float32, device=q_dev.device)
+        xchg = self._exchange(q_dev.device) if (k <= 32 and B <= 4096 and B * k <= 131072) else None
+        if xchg is not None:
+            lib = _native.load()
+            rc = lib.cslam_nns_xchg_merge(xchg, ctypes.c_void_p(keys.data_ptr()), B, k, 3,
+                                          ctypes.c_void_p(out_idx.data_ptr()), ctypes.c_void_p(out_sim.data_ptr()),
+                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+            if rc != _native.OK:
+                raise _native.NativeError(rc, lib.cslam_nns_xchg_last_error(xchg).decode("utf-8", "replace"))
+            return out_idx, out_sim
         if self.world > 1:
             gathered = torch.empty((self.world, B, k), dtype=torch.int64, device=q_dev.device)
             dist.all_gather_into_tensor(gathered, keys, group=self.group)
         else:
             gathered = keys.view(1, B, k)
-        if out_idx is None:
-            out_idx = torch.empty((B, k), dtype=torch.int64, device=q_dev.device)
-            out_sim = torch.empty((B, k), dtype=torch.float32, device=q_dev.device)
         lib = _native.load()
         rc = lib.cslam_nns_merge_keys(q_dev.device.index, ctypes.c_void_p(gathered.data_ptr()),
                                       self.world, B, k, ctypes.c_void_p(out_idx.data_ptr()),

@@ -111,6 +111,34 @@ int cslam_nns_merge_keys(int device, const uint64_t* keys_dev, int parts, int64_
                          int64_t* out_idx, float* out_sim, int dst_is_device, void* stream,
                          int64_t* out_kk);
 
+/* -- exchange step of the sharded search as one kernel over NVLink peer memory -------- */
+/* Replaces "all-gather of the packed keys (NCCL) + cslam_nns_merge_keys" by ONE kernel: every rank stores its
+ * per-query keys directly into every rank's exchange buffer (peer memory opened once with CUDA IPC),
+ * publishes them with release stores, waits for the other ranks' flags and merges.  The reference has no
+ * multi-GPU path; the caller is cslam_b200/sharded.py.  One process per GPU, all ranks make the same calls. */
+typedef struct cslam_nns_xchg_s* cslam_nns_xchg_t;
+const char* cslam_nns_xchg_last_error(cslam_nns_xchg_t x);
+/* Allocate this rank's exchange buffers on `device` (world <= 8). */
+int cslam_nns_xchg_create(int device, int world, int rank, cslam_nns_xchg_t* out);
+int cslam_nns_xchg_destroy(cslam_nns_xchg_t x);
+/* 128 opaque bytes (two CUDA IPC memory handles) that the other ranks need to reach this rank's buffers;
+ * the caller exchanges them (e.g. one all_gather at start-up). */
+int cslam_nns_xchg_export(cslam_nns_xchg_t x, void* handle128);
+/* `handles`: world x 128 bytes, entry r exported by rank r (the own entry is ignored). */
+int cslam_nns_xchg_connect(cslam_nns_xchg_t x, const void* handles);
+/* Same, for `world` exchange objects living in ONE process (single-GPU emulation in the tests). */
+int cslam_nns_xchg_connect_local(cslam_nns_xchg_t x, const cslam_nns_xchg_t* all);
+/* local_keys_dev: this rank's [B][k] packed keys (cslam_nns_search_keys).  Writes the merged global rows and
+ * similarities [B][k] to device memory (-1 / -inf past the end).  k <= 32, B <= 4096, B * k <= 131072.
+ * phase: 3 = push + wait + merge (production); 1 = push only, 2 = wait + merge only (tests, where one GPU
+ * plays every rank and no launch may wait for another).  Stream-ordered, no host synchronisation.  A peer
+ * that does not arrive within CSLAM_NNS_XCHG_TIMEOUT_S (20 s) makes the NEXT call fail with
+ * CSLAM_NNS_ECUDA instead of hanging the GPU. */
+int cslam_nns_xchg_merge(cslam_nns_xchg_t x, const uint64_t* local_keys_dev, int64_t B, int k, int phase,
+                         int64_t* out_idx_dev, float* out_sim_dev, void* stream);
+/* 0, or CSLAM_NNS_ECUDA when an earlier call timed out waiting for a peer (read after a stream sync). */
+int cslam_nns_xchg_status(cslam_nns_xchg_t x);
+
 /* -- tuning / diagnostics ----------------------------------------------------------------------- */
 
 /* Force a search variant for tests and profiling: 0 = automatic, 1 = single-query kernel looped,

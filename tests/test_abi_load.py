@@ -26,7 +26,8 @@ def test_library_exports_every_declared_symbol():
     assert len(declared) >= 18
     for name in declared:
         assert hasattr(lib, name), name
-    assert set(declared) == set(_native.SIGNATURES), "ctypes table out of sync with the header"
+    assert set(declared) == set(_native.SIGNATURES) | set(_native.XCHG_SIGNATURES), \
+        "ctypes table out of sync with the header"
     assert lib.cslam_nns_abi_version() == 1
 
 
@@ -34,6 +35,16 @@ def test_library_has_no_libcuda_link_dependency():
     # the driver API is reached through cudaGetDriverEntryPoint so the .so loads without a driver
     out = os.popen("ldd %s" % _native.LIB_PATH).read()
     assert "libcuda.so" not in out and "libtorch" not in out
+
+
+@pytest.mark.skipif(HAS_GPU, reason="checks the no-GPU failure mode")
+def test_exchange_create_fails_loudly_without_gpu():
+    lib = _native.load()
+    x = ctypes.c_void_p()
+    assert lib.cslam_nns_xchg_create(0, 2, 0, ctypes.byref(x)) == _native.ENODEV
+    assert not x.value
+    assert lib.cslam_nns_xchg_create(0, 9, 0, ctypes.byref(x)) == _native.EINVAL   # world <= 8
+    assert b"cslam_nns_xchg_create" in lib.cslam_nns_xchg_last_error(None)
 
 
 @pytest.mark.skipif(HAS_GPU, reason="checks the no-GPU failure mode")

@@ -1,0 +1,94 @@
+#!/usr/bin/env python
+"""Row-sharded search across REAL ranks (run under torchrun, one process per GPU):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29611 tools/sharded_check.py
+
+The peer-memory exchange kernel (K5) must give bit-identical results to the NCCL all-gather + K4 route and
+to an unsharded search of the whole database; both routes are timed with CUDA events (max over ranks)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import synth  # noqa: E402
+from cslam_b200 import NearestNeighborsMatching  # noqa: E402
+from cslam_b200.sharded import ShardedNearestNeighborsMatching  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl")
+    dev = torch.device("cuda", torch.cuda.current_device())
+    bad = 0
+    for n, d, shapes in [(20011, 256, [(256, 10), (37, 1), (1, 32), (256, 10)]),
+                         (300000, 512, [(256, 10), (16, 10)])]:
+        db = synth.unit_rows(7 + n, n, d)
+        peer = ShardedNearestNeighborsMatching(exchange="peer")
+        nccl = ShardedNearestNeighborsMatching(exchange="nccl")
+        for m in (peer, nccl):
+            m.add_items(torch.from_numpy(db), list(range(n)))
+        whole = None
+        if rank == 0:
+            whole = NearestNeighborsMatching()
+            whole.add_items(torch.from_numpy(db), list(range(n)))
+        for B, k in shapes:
+            q = torch.from_numpy(synth.queries_for(n + B + k, db, B)).to(dev)
+            ia, sa = peer.search_batch_device(q, k)
+            ib, sb = nccl.search_batch_device(q, k)
+            torch.cuda.synchronize()
+            same = torch.equal(ia, ib) and torch.equal(sa, sb)
+            used_peer = peer._xchg is not None
+            detail = ""
+            if not same:
+                detail += " [rank %d peer!=nccl: %d idx, %d sims differ]" % (
+                    rank, int((ia != ib).sum()), int((sa != sb).sum()))
+            if rank == 0:
+                wi, ws = whole._search_block(q, k)
+                pi, ps = ia.cpu().numpy(), sa.cpu().numpy()
+                if not (np.array_equal(wi, pi) and np.array_equal(ws, ps)):
+                    same = False
+                    j = int(np.argmax((wi != pi).any(axis=1) | (ws != ps).any(axis=1)))
+                    detail += " [peer!=unsharded: %d idx, %d sims differ, max |dsim| %.3g; q%d whole %s %s peer %s %s]" % (
+                        int((wi != pi).sum()), int((ws != ps).sum()), float(np.abs(ws - ps).max()), j,
+                        wi[j].tolist(), ws[j].tolist(), pi[j].tolist(), ps[j].tolist())
+            if detail:
+                print(detail, flush=True)
+            ok = torch.tensor([1 if (same and used_peer) else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            times = []
+            for m in (peer, nccl):
+                for _ in range(5):
+                    m.search_batch_device(q, k)
+                dist.barrier()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(50):
+                    m.search_batch_device(q, k)
+                e1.record()
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) / 50], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                times.append(float(t.item()))
+            if rank == 0:
+                print("n=%d d=%d B=%d k=%d world=%d: %s   step %.4f ms peer-memory kernel, %.4f ms all-gather + K4"
+                      % (n, d, B, k, world, "identical" if int(ok.item()) else "MISMATCH", times[0], times[1]),
+                      flush=True)
+            bad += 0 if int(ok.item()) else 1
+        del peer, nccl, whole
+    if rank == 0:
+        print("SHARDED CHECK", "FAILED" if bad else "OK", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(1 if bad else 0)
+
+
+if __name__ == "__main__":
+    main()
