@@ -212,6 +212,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
       : "memory");
 }
 
+// same, with an L2 eviction-priority hint (createpolicy-encoded 64-bit policy)
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar,
+                                              unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+          "r"(smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+
 // 2-D tiled TMA load (SASS: UTMALDG).  c0 = innermost (column) coordinate, c1 = row coordinate.
 __device__ __forceinline__ void tma_load_2d(void* dst, const void* tmap, int c0, int c1,
                                             uint64_t* bar) {
