@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="override the batch size (debugging only)")
     ap.add_argument("--k", type=int, default=0, help="override k (debugging only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-torch-bar", action="store_true",
+                    help="skip the stock torch-on-CUDA restatement of the reference's search (N=1 only)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -141,6 +143,37 @@ class ClockSampler(threading.Thread):
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(self.reasons)}
+
+
+def torch_cuda_bar(view, q_block, k):
+    """The reference's search arithmetic (cslam/nns_matching.py:57-63: cosine_similarity over the stored
+    rows, full argsort, gather, two device->host reads) restated with stock torch ops on the SAME device and
+    the same resident database (the zero-copy `.data` view), one query at a time as the reference's API is.
+    /root/reference itself cannot travel to the benchmark box; this is PyTorch library code used as a bar,
+    never part of the product path.  A few queries are timed and the rate is per query."""
+    import torch
+
+    def one(q):
+        sim = torch.nn.functional.cosine_similarity(view, q.view(1, -1))
+        order = torch.argsort(sim, descending=True)[:k]
+        return order.cpu().numpy(), sim[order].cpu().numpy()
+
+    nq, nb_ = 4, int(q_block.shape[0])
+    try:
+        one(q_block[0])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for j in range(nq):
+            one(q_block[j % nb_])
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / nq
+    except RuntimeError as e:  # e.g. out of memory for the similarity temporaries
+        return {"value": None, "unit": "queries/s", "kind": "port", "sample": "failed: %s" % str(e)[:80]}
+    finally:
+        torch.cuda.empty_cache()
+    return {"value": 1.0 / dt, "unit": "queries/s", "kind": "port",
+            "sample": "%d single-query searches (torch %s: cosine_similarity + argsort + gather + 2 D2H reads), "
+                      "same device, same resident database" % (nq, torch.__version__)}
 
 
 def measured_peaks():
@@ -375,6 +408,11 @@ def main():
         e2e = {"value": args.steps * batch / float(t.item()), "unit": "queries/s",
                "h2d_bytes_per_step": batch * dim * 4, "d2h_bytes_per_step": batch * k * 12}
 
+    # ---- the reference's own GPU arithmetic on the same box (informational bar, SURVEY §8 d3 iii) ------
+    torch_bar = None
+    if world == 1 and not args.no_torch_bar:
+        torch_bar = torch_cuda_bar(m.local.data[:m.local.n], qb[0], k)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -433,6 +471,8 @@ def main():
                            **({"exchange": "K5 peer-memory kernel (csrc/k5_exchange.cu)"
                                if getattr(m, "_xchg", None) is not None else "NCCL all-gather + K4"} if world > 1 else {})),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches)}
+    if torch_bar is not None:
+        line["torch_cuda_reference"] = torch_bar
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
