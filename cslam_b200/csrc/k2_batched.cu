@@ -41,7 +41,9 @@ namespace {
 constexpr int BM = 128;          // database rows per tile (UMMA M)
 constexpr int BK = 32;           // floats per K block = 128 bytes = one swizzle row
 constexpr int kEpiThreads = 128, kConvThreads = 128;
-constexpr int kThreads = 352;    // 4 epilogue + 4 converter warps, X producer, MMA issuer, Q producer
+constexpr int kConvGroups = 2;   // converter warp groups, alternating K blocks (warps 4-7 and 12-15)
+constexpr int kThreads = 512;    // warps 0-3 epilogue, 4-7 converter group 0, 8 X producer, 9 MMA issuer,
+                                 // 10 Q producer, 11 idle, 12-15 converter group 1
 constexpr int kQueueCap = 512;   // per epilogue warp and 16-query chunk: 4 queries x 128 rows
 constexpr int kTmemCols = 512;
 constexpr int kMaxXSlots = 8;    // raw database tiles in flight (shared memory)
@@ -84,7 +86,7 @@ __host__ __device__ inline Smem carve(int BN, int B, int k, int xslots, int aslo
   s.qpar_off = o;   o += (uint32_t)BN * 16;  // per query {mean(q), 1/|q|, threshold (ordered uint), -}
   s.queue_off = o;  o += 4u * kQueueCap * 8;
   s.qcnt_off = o;   o += 16;
-  s.norm_off = o;   o += 4u * BM * 4;  // [2][BM] |x|^2 then [2][BM] sum(x)
+  s.norm_off = o;   o += 4u * kConvGroups * BM * 4;  // [2][groups][BM] partial |x|^2, then the same for sum(x)
   o = (o + 7u) & ~7u;
   s.bars_off = o;   o += 40u * 8;      // see the barrier table in the kernel
   s.tmem_off = o;   o += 16;
@@ -124,7 +126,7 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   u64* queue = reinterpret_cast<u64*>(smem + L.queue_off);
   int* qcnt = reinterpret_cast<int*>(smem + L.qcnt_off);
   float* norms = reinterpret_cast<float*>(smem + L.norm_off);
-  float* sums = norms + 2 * BM;
+  float* sums = norms + 2 * kConvGroups * BM;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars_off);
   uint64_t* x_full = bars;               // [SX] raw tile landed (TMA)                   X producer -> converter
   uint64_t* x_empty = bars + 8;          // [SX] raw tile is in registers                converter  -> X producer
@@ -155,7 +157,7 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
       mbar_init(&acc_empty[a], kEpiThreads);
-      mbar_init(&norm_bar[a], kConvThreads);
+      mbar_init(&norm_bar[a], kConvThreads * kConvGroups);
     }
     mbar_fence_init();
   }
@@ -242,12 +244,15 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         __syncwarp();
       }
     }
-  } else if (warp >= 4 && warp < 8) {
+  } else if ((warp >= 4 && warp < 8) || warp >= 12) {
     // ===== converter: raw tile (smem) -> x_hi, x_lo (tensor memory), row norms ========================
+    // Two groups of 4 warps take alternate K blocks (group = kb & 1, so a row's partial sums do not depend on
+    // its tile or shard): one group alone costs ~12 % over the HBM time of a block.
     // Thread r owns tile row r == TMEM lane r (warp w may only address lanes 32*(w%4)..+31, and 4 % 4 == 0).
     // The split tiles never touch shared memory: that removes the two 16 KB stores and the three 16 KB
     // operand fetches per K block that kept the shared-memory pipe ~90% busy (profiles/r1_k2rows_*).
-    const int r = tid - 4 * 32;
+    const int g = warp >= 12 ? 1 : 0;
+    const int r = (warp & 3) * 32 + lane;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     int sx = 0, sa = 0;
     uint32_t phx = 0, pha = 0;
@@ -255,6 +260,11 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const int a = (int)(t & 1);
       float nn = 0.f, sum = 0.f;
       for (int kb = 0; kb < p.kblocks; ++kb) {
+        if ((kb & 1) != g) {  // the other group's block: only keep the ring positions in step
+          sx = sx + 1 == SX ? 0 : sx + 1; phx ^= (sx == 0);
+          sa = sa + 1 == SA ? 0 : sa + 1; pha ^= (sa == 0);
+          continue;
+        }
         uint32_t hi[BK], lo[BK];
         mbar_wait(&x_full[sx], phx);
         if (!(p.dbg & 1)) {
@@ -292,11 +302,11 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       }
       // the epilogue of tile t-2 must be done with norms[a] before it is overwritten
       mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
-      norms[a * BM + r] = nn;
-      sums[a * BM + r] = sum;
+      norms[(a * kConvGroups + g) * BM + r] = nn;
+      sums[(a * kConvGroups + g) * BM + r] = sum;
       mbar_arrive(&norm_bar[a]);
     }
-  } else {
+  } else if (warp < 4) {
     // ===== epilogue: TMEM -> similarities -> per-query top-k ========================================
     const int r = tid;  // accumulator lane == tile row; warp w may only touch lanes 32w .. 32w+31
     const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
@@ -316,8 +326,9 @@ k2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       if (g_new > 1u && g_new - 1u > qpar[tid].z) qpar[tid].z = g_new - 1u;
       const bool row_ok = row0 + r < p.n;
       // 1 / max(|x|, eps)  ==  rsqrt(max(|x|^2, eps^2))
-      const float inv_nx = rsqrtf(fmaxf(norms[a * BM + r], kEps * kEps));
-      const float sum_x = sums[a * BM + r];
+      const float inv_nx = rsqrtf(fmaxf(norms[(a * kConvGroups) * BM + r] + norms[(a * kConvGroups + 1) * BM + r],
+                                        kEps * kEps));
+      const float sum_x = sums[(a * kConvGroups) * BM + r] + sums[(a * kConvGroups + 1) * BM + r];
       for (int c0 = 0; c0 < ((p.dbg & 4) ? 0 : p.BN); c0 += 16) {
         uint32_t v[16];
         tmem_ld_32x32b_x16(tmem_base + lane_base + (uint32_t)(a * p.BN + c0), v);
