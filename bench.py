@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Headline benchmark: NN-search queries/s on the configuration BASELINE.json's metric is quoted on.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c4|c5]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c4|c5|swarm|sc]
 
 Default workload ``c3`` = BASELINE.json configs[2]: 1M x 4096 fp32 descriptors, batches of 256
 queries, top-10 (the "1M x 4096 DB" the metric names).  One *step* = one batch of 256 queries
@@ -46,7 +46,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + ["sc"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + ["sc", "swarm"])
+    ap.add_argument("--robots", type=int, default=8, help="swarm workload: number of robots R")
     ap.add_argument("--rows", type=int, default=0, help="override the row count (debugging only)")
     ap.add_argument("--dim", type=int, default=0, help="override the descriptor size (debugging only)")
     ap.add_argument("--batch", type=int, default=0, help="override the batch size (debugging only)")
@@ -269,10 +270,108 @@ def bench_scancontext(args):
     print(json.dumps(line))
 
 
+def bench_swarm(args):
+    """SURVEY §8 d1 C4 in its swarm form + f1/f2: R robots (default 8), the 2M x 256 database of BASELINE
+    configs[3] split into R per-robot databases of 2M/R rows.  One step = one local keyframe through the
+    drop-in ``LoopClosureSparseMatching.add_local_global_descriptor`` (1 add_item on the local database +
+    R-1 search_best on the other robots' databases, threshold test, edge bookkeeping) — host descriptor in,
+    host matches out, so the whole leg is end to end.  Timed twice on the same object: through
+    ``search_best_multi`` (one staging, R-1 kernels back to back, ONE synchronisation; the default) and
+    through the reference's per-robot loop (R-1 synchronised searches)."""
+    import numpy as np
+    import torch
+    from cslam_b200 import _native
+    from cslam_b200.loop_closure_sparse_matching import CandidateEdges, LoopClosureSparseMatching
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    lib = _native.load()
+    R, dim = args.robots, args.dim or 256
+    rows = args.rows or 2_000_000
+    per = rows // R
+    params = {"robot_id": 0, "max_nb_robots": R, "frontend.sensor_type": "stereo",
+              "frontend.similarity_threshold": 0.9, "frontend.nb_best_matches": 10,
+              "frontend.intra_loop_min_inbetween_keyframes": 20}
+    lcsm = LoopClosureSparseMatching(params, candidate_selector=CandidateEdges(0, R))
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(4)
+    probe = None
+    for r in range(R):
+        x = torch.rand((per, dim), generator=gen, device=dev, dtype=torch.float32)
+        x /= x.norm(dim=1, keepdim=True)
+        (lcsm.local_nnsm if r == 0 else lcsm.other_robots_nnsm[r]).add_items(x, list(range(per)))
+        if r == 1:
+            probe = x[:4096].cpu().numpy()
+        del x
+    nq = args.warmup + args.steps
+    rng = np.random.default_rng(5)
+    qs = rng.random((nq, dim)).astype(np.float32)
+    qs[::4] = probe[: len(qs[::4])] + 0.02 * rng.standard_normal((len(qs[::4]), dim)).astype(np.float32)
+    qs /= np.linalg.norm(qs, axis=1, keepdims=True)          # every 4th keyframe revisits a place of robot 1
+
+    def run(fused, lo, hi):
+        lcsm._dense = fused       # False -> the reference's per-robot loop over search_best
+        n_match = 0
+        for i in range(lo, hi):
+            n_match += len(lcsm.add_local_global_descriptor(qs[i], per + i))
+        return n_match
+
+    out = {}
+    for name, fused in (("loop", False), ("multi", True)):
+        run(fused, 0, args.warmup)
+        torch.cuda.synchronize()
+        sampler = ClockSampler(0)
+        sampler.start()
+        l0 = lib.cslam_nns_launch_count()
+        t0 = time.perf_counter()
+        nm = run(fused, args.warmup, nq)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        out[name] = {"s_per_step": dt / args.steps, "matches": nm, "launches": lib.cslam_nns_launch_count() - l0,
+                     "clocks": sampler.stop()}
+    assert out["loop"]["matches"] == out["multi"]["matches"]
+    lcsm._dense = True
+    hbm_peak, _, _, which = measured_peaks()
+    dt = out["multi"]["s_per_step"]
+    bytes_ = float(R - 1) * per * dim * 4
+    cpu = None
+    if not args.no_cpu_baseline:
+        v, cores, desc = cpu_port_qps(per, dim, 1, 1)
+        cpu = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port", "sample": desc}
+    qps = (R - 1) / dt
+    line = {"metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[3] as a swarm: %d robots, %d x %d fp32 per robot database, one "
+                                   "step = add_local_global_descriptor (1 add_item + %d search_best + threshold)"
+                                   % (R, per, dim, R - 1),
+                       "rows": per * R, "dim": dim, "batch": 1, "k": 1, "robots": R,
+                       "l2": "the %d databases searched per step total %.2f GB, far larger than the 126 MB L2; no "
+                             "flush needed" % (R - 1, bytes_ / 1e9)},
+            "roofline": {"bound": "hbm", "achieved": bytes_ / dt / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": bytes_ / dt / 1e9 / hbm_peak, "traffic": None, "kernel": "k1_single_query",
+                         "note": "END-TO-END figure: (R-1) * rows * ld * 4 algorithmic bytes per step / wall time of "
+                                 "the whole Python call (H2D of the row and the query, R-1 kernels, one sync, edge "
+                                 "bookkeeping); peak = %s copy bandwidth" % which},
+            "cpu_baseline": cpu,
+            "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 2 * dim * 4,
+                    "d2h_bytes_per_step": (R - 1) * 12},
+            "per_robot_loop": {"value": (R - 1) / out["loop"]["s_per_step"], "unit": "queries/s",
+                               "ms_per_step": out["loop"]["s_per_step"] * 1e3,
+                               "note": "same kernels through the reference's loop of R-1 synchronised search_best calls"},
+            "clocks": out["multi"]["clocks"], "gpu_launches": int(out["multi"]["launches"]),
+            "matches": out["multi"]["matches"]}
+    print(json.dumps(line))
+
+
 def main():
     args = parse()
     if args.workload == "sc":
         return bench_scancontext(args)
+    if args.workload == "swarm":
+        if args.impl == "reference":   # the CPU arm of one per-robot database: BASELINE configs[3]'s shape
+            args.workload = "c4"
+            return reference_arm(args, (args.rows or 2_000_000) // args.robots, args.dim or 256, 1, 1)
+        return bench_swarm(args)
     rows, dim, batch, k, _ = WORKLOADS[args.workload]
     if args.rows:
         rows = args.rows

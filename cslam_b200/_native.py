@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "_lib", "libcslam_nns.so")
 
 OK = 0
 EINVAL, ENODEV, ENOMEM, ECUDA, ESTATE = -1, -2, -3, -4, -5
+FILTER_BEST, FILTER_INTRA = 0, 1  # CSLAM_NNS_FILTER_*
 
 _c = ctypes
 _handle = _c.c_void_p
@@ -38,6 +39,12 @@ SIGNATURES = {
                                  _c.POINTER(_i64)]),
     "cslam_nns_search": (_c.c_int, [_handle, _f32p, _i64, _i64, _c.c_int, _c.c_int, _i64p, _f32p,
                                     _c.c_int, _c.c_void_p, _c.POINTER(_i64)]),
+    "cslam_nns_search_multi": (_c.c_int, [_c.POINTER(_handle), _c.c_int, _f32p, _i64, _c.c_int, _c.c_int,
+                                          _i64p, _f32p, _i64p, _c.c_void_p]),
+    "cslam_nns_set_row_ids": (_c.c_int, [_handle, _i64, _i64, _i64p]),
+    "cslam_nns_search_filtered": (_c.c_int, [_handle, _f32p, _i64, _i64, _c.c_int, _c.c_int, _c.c_int,
+                                             _i64p, _i64, _c.c_float, _i64p, _f32p, _c.c_void_p,
+                                             _c.c_void_p, _c.POINTER(_i64)]),
     "cslam_nns_search_keys": (_c.c_int, [_handle, _f32p, _i64, _i64, _c.c_int, _c.c_int, _i64, _i64,
                                          _c.c_void_p, _c.c_void_p]),
     "cslam_nns_merge_keys": (_c.c_int, [_c.c_int, _c.c_void_p, _c.c_int, _i64, _c.c_int, _i64p,

@@ -89,8 +89,12 @@ struct cslam_nns_s {
   int variant = 0, last_variant = 0;
   K1Tuning k1;
   // device scratch
-  DevBuf q, q_lo, inv_qn, scratch, ticket, part_keys, res_dev, all_sims, sort_tmp, sort_kv;
+  DevBuf q, q_lo, inv_qn, scratch, ticket, part_keys, res_dev, all_sims, sort_tmp, sort_kv, qids;
   PinBuf res_host;
+  // integer row identities for the device-side candidate filter (cslam_nns_search_filtered)
+  Arena ids_arena;
+  std::vector<long long> ids_host;
+  long long ids_synced = 0;  // rows [0, ids_synced) of ids_host are in ids_arena
   // optional per-kernel timing (cslam_nns_profile)
   bool profile = false;
   std::vector<cudaEvent_t> ev;   // pairs
@@ -167,6 +171,60 @@ __global__ void fill_kernel(long long* idx, float* sim, long long B, int k, int 
   const int j = from + (int)(i - b * w);
   if (idx) idx[b * k + j] = -1;
   if (sim) sim[b * k + j] = -INFINITY;
+}
+
+// Candidate filter of the reference's callers, one thread per query.  Reads the top-k
+// (rows, sims) the search left in device memory, maps rows to keyframe ids through the device id table
+// and applies loop_closure_sparse_matching.py:51,71 (mode 0) or :83-97 (mode 1).  Results go to the
+// caller's (mapped pinned) arrays with pitch k; entries past k_run are filled.
+__global__ void filter_kernel(const long long* __restrict__ idx, const float* __restrict__ sim,
+                              long long B, int k_run, int k, const long long* __restrict__ row_ids,
+                              const long long* __restrict__ qids, long long qid0, int has_qid, int mode,
+                              long long min_gap, float thr, long long* o_idx, float* o_sim, int* o_pos) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const long long qid = qids ? qids[b] : qid0;
+  int pos = -1;
+  for (int j = 0; j < k_run; ++j) {
+    const long long r = idx[b * k_run + j];
+    const float s = sim[b * k_run + j];
+    o_idx[b * k + j] = r;
+    o_sim[b * k + j] = s;
+    if (pos >= 0 || r < 0) continue;
+    if (mode == CSLAM_NNS_FILTER_BEST) {
+      if (j == 0 && s >= thr) pos = 0;  // :51,:71 (a NaN similarity does not pass `>=`)
+      continue;
+    }
+    if (has_qid) {
+      const long long id = row_ids[r];
+      if (j == 0 && id == qid) continue;  // :83-84 kfs[0] == kf_id -> dropped
+      long long gap = id - qid;
+      if (gap < 0) gap = -gap;
+      if (gap < min_gap) continue;        // :89-91
+    }
+    if (s < thr) continue;                // :93-94 (a NaN similarity is not skipped by `<`)
+    pos = j;
+  }
+  for (int j = k_run; j < k; ++j) {
+    o_idx[b * k + j] = -1;
+    o_sim[b * k + j] = -INFINITY;
+  }
+  o_pos[b] = pos;
+}
+
+// Bring the device id table up to date with ids_host (rows [ids_synced, n)).
+int sync_row_ids(cslam_nns_t h, cudaStream_t stream) {
+  if ((long long)h->ids_host.size() < h->n)
+    return fail(h, CSLAM_NNS_ESTATE, "row ids missing: cslam_nns_set_row_ids must cover every row");
+  if (h->ids_synced >= h->n) return 0;
+  std::string err;
+  if (!h->ids_arena.ensure(h->device, (size_t)h->capacity * 8, stream, &err))
+    return fail(h, CSLAM_NNS_ENOMEM, err);
+  long long* dst = (long long*)h->ids_arena.base();
+  CK(h, cudaMemcpyAsync(dst + h->ids_synced, h->ids_host.data() + h->ids_synced,
+                        (size_t)(h->n - h->ids_synced) * 8, cudaMemcpyHostToDevice, stream));
+  h->ids_synced = h->n;
+  return 0;
 }
 
 // Run the search for B device-resident queries (pitch q_ld) and write k_run entries per query to
@@ -367,7 +425,8 @@ int cslam_nns_destroy(cslam_nns_t h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     h->arena.release();
-    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket,
+    h->ids_arena.release();
+    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket, &h->qids,
                       &h->part_keys, &h->res_dev, &h->all_sims, &h->sort_tmp, &h->sort_kv};
     for (DevBuf* b : bufs) b->free();
     h->res_host.free();
@@ -492,6 +551,131 @@ int cslam_nns_search(cslam_nns_t h, const float* queries, int64_t B, int64_t q_l
       for (int j = k_run; j < k; ++j) out_sim[b * k + j] = -std::numeric_limits<float>::infinity();
     }
   }
+  return 0;
+}
+
+int cslam_nns_search_multi(const cslam_nns_t* hs, int count, const float* query, int64_t q_len,
+                           int src_is_device, int k, int64_t* out_idx, float* out_sim, int64_t* out_kk,
+                           void* stream_) {
+  if (!hs || count <= 0) {
+    g_create_error = "cslam_nns_search_multi: no handles";
+    return CSLAM_NNS_EINVAL;
+  }
+  cslam_nns_t h0 = nullptr;  // first searchable database: owns the staging and result buffers
+  for (int i = 0; i < count; ++i) {
+    cslam_nns_t h = hs[i];
+    if (!h || h->dim <= 0 || h->n == 0) continue;
+    if (!h0) h0 = h;
+    else if (h->device != h0->device || h->dim != h0->dim)
+      return fail(h0, CSLAM_NNS_EINVAL, "cslam_nns_search_multi: databases differ in device or dim");
+  }
+  const float ninf = -std::numeric_limits<float>::infinity();
+  if (k < 0 || (h0 && !query)) return fail(h0, CSLAM_NNS_EINVAL, "bad query/k");
+  for (long long i = 0; i < (long long)count * k; ++i) {
+    if (out_idx) out_idx[i] = -1;
+    if (out_sim) out_sim[i] = ninf;
+  }
+  if (out_kk) for (int i = 0; i < count; ++i) out_kk[i] = 0;
+  if (!h0 || k == 0) return 0;
+  if (q_len < h0->dim) return fail(h0, CSLAM_NNS_EINVAL, "query shorter than dim");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h0->device);
+  const float* dq;
+  long long dq_ld;
+  int rc = stage_queries(h0, query, 1, q_len, src_is_device, stream, &dq, &dq_ld);
+  if (rc) return rc;
+  if (!h0->res_host.ensure((size_t)count * k * 12)) return fail(h0, CSLAM_NNS_ENOMEM, "pinned result buffer");
+  long long* hi = (long long*)h0->res_host.p;
+  float* hsim = (float*)(hi + (size_t)count * k);
+  std::vector<int> kks(count, 0);
+  for (int i = 0; i < count; ++i) {
+    cslam_nns_t h = hs[i];
+    if (!h || h->dim <= 0 || h->n == 0) continue;
+    kks[i] = (int)(k < h->n ? k : h->n);
+    rc = search_device(h, dq, 1, dq_ld, kks[i], nullptr, hi + (size_t)i * k, hsim + (size_t)i * k, 1, 0, stream);
+    if (rc) {
+      if (h != h0) h0->err = h->err;
+      cudaStreamSynchronize(stream);
+      return rc;
+    }
+  }
+  CK(h0, cudaStreamSynchronize(stream));
+  for (int i = 0; i < count; ++i) {
+    if (out_idx) memcpy(out_idx + (size_t)i * k, hi + (size_t)i * k, (size_t)kks[i] * 8);
+    if (out_sim) memcpy(out_sim + (size_t)i * k, hsim + (size_t)i * k, (size_t)kks[i] * 4);
+    if (out_kk) out_kk[i] = kks[i];
+  }
+  return 0;
+}
+
+int cslam_nns_set_row_ids(cslam_nns_t h, int64_t first_row, int64_t count, const int64_t* ids) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (first_row < 0 || count < 0 || (count > 0 && !ids)) return fail(h, CSLAM_NNS_EINVAL, "bad ids/range");
+  if (first_row > (long long)h->ids_host.size()) return fail(h, CSLAM_NNS_EINVAL, "row ids would leave a gap");
+  if ((long long)h->ids_host.size() < first_row + count) h->ids_host.resize((size_t)(first_row + count));
+  for (long long i = 0; i < count; ++i) h->ids_host[(size_t)(first_row + i)] = ids[i];
+  if (count > 0 && first_row < h->ids_synced) h->ids_synced = first_row;  // overwritten: upload again
+  return 0;
+}
+
+int cslam_nns_search_filtered(cslam_nns_t h, const float* queries, int64_t B, int64_t q_ld,
+                              int src_is_device, int k, int mode, const int64_t* query_ids,
+                              int64_t min_gap, float threshold, int64_t* out_idx, float* out_sim,
+                              int32_t* out_match_pos, void* stream_, int64_t* out_kk) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (B < 0 || k < 0 || (B > 0 && !queries)) return fail(h, CSLAM_NNS_EINVAL, "bad queries/B/k");
+  if (mode != CSLAM_NNS_FILTER_BEST && mode != CSLAM_NNS_FILTER_INTRA)
+    return fail(h, CSLAM_NNS_EINVAL, "unknown filter mode");
+  if (B > 0 && (!out_match_pos || (k > 0 && (!out_idx || !out_sim))))
+    return fail(h, CSLAM_NNS_EINVAL, "output arrays are required");
+  if (k > kK1MaxK) return fail(h, CSLAM_NNS_EINVAL, "filtered search supports k <= 128");
+  if (h->dim <= 0) return fail(h, CSLAM_NNS_ESTATE, "descriptor size not set");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h->device);
+  const long long kk = k < h->n ? k : h->n;
+  if (out_kk) *out_kk = kk;
+  if (B == 0) return 0;
+  if (kk == 0) {
+    for (long long i = 0; i < B * k; ++i) {
+      out_idx[i] = -1;
+      out_sim[i] = -std::numeric_limits<float>::infinity();
+    }
+    for (long long b = 0; b < B; ++b) out_match_pos[b] = -1;
+    return 0;
+  }
+  const int k_run = (int)kk;
+  const bool need_ids = mode == CSLAM_NNS_FILTER_INTRA && query_ids != nullptr;
+  int rc = need_ids ? sync_row_ids(h, stream) : 0;
+  if (rc) return rc;
+  const float* dq;
+  long long dq_ld;
+  rc = stage_queries(h, queries, B, q_ld, src_is_device, stream, &dq, &dq_ld);
+  if (rc) return rc;
+  if (!h->res_dev.ensure((size_t)B * k_run * 12)) return fail(h, CSLAM_NNS_ENOMEM, "result buffer");
+  if (!h->res_host.ensure((size_t)B * k * 12 + (size_t)B * 4)) return fail(h, CSLAM_NNS_ENOMEM, "pinned result buffer");
+  long long* di = (long long*)h->res_dev.p;
+  float* ds = (float*)(di + B * k_run);
+  rc = search_device(h, dq, B, dq_ld, k_run, nullptr, di, ds, 1, 0, stream);
+  if (rc) return rc;
+  const long long* dqids = nullptr;
+  if (need_ids && B > 1) {  // one query's id travels as a kernel argument
+    if (!h->qids.ensure((size_t)B * 8)) return fail(h, CSLAM_NNS_ENOMEM, "query id buffer");
+    CK(h, cudaMemcpyAsync(h->qids.p, query_ids, (size_t)B * 8, cudaMemcpyHostToDevice, stream));
+    dqids = (const long long*)h->qids.p;
+  }
+  long long* hi = (long long*)h->res_host.p;
+  float* hsim = (float*)(hi + B * k);
+  int* hpos = (int*)(hsim + B * k);
+  filter_kernel<<<(unsigned)((B + 127) / 128), 128, 0, stream>>>(
+      di, ds, B, k_run, k, (const long long*)h->ids_arena.base(), dqids,
+      need_ids ? (long long)query_ids[0] : 0ll, need_ids ? 1 : 0, mode, (long long)min_gap, threshold,
+      hi, hsim, hpos);
+  count_launch();
+  CK(h, cudaGetLastError());
+  CK(h, cudaStreamSynchronize(stream));
+  memcpy(out_idx, hi, (size_t)B * k * 8);
+  memcpy(out_sim, hsim, (size_t)B * k * 4);
+  memcpy(out_match_pos, hpos, (size_t)B * 4);
   return 0;
 }
 

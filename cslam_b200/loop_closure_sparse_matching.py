@@ -11,13 +11,17 @@ compared edge by edge.
 
 Additive: ``add_other_robot_global_descriptors`` handles one whole
 ``GlobalDescriptors`` message (<= 10 descriptors, ``global_descriptor_loop_closure_detection.py:388-404``)
-with ONE batched search instead of one search per descriptor.
+with ONE batched search instead of one search per descriptor, and ``add_local_global_descriptor``
+searches the R-1 other robots' databases through ``search_best_multi`` (one staging, one synchronisation).
+Additive: the threshold / self-hit / min-gap filter of ``:51,71,83-97`` runs on the device
+(``NearestNeighborsMatching.search_candidates``) whenever the keyframe ids are ints; results are identical.
 """
 from typing import NamedTuple
 
 import numpy as np
 import torch
 
+from ._native import FILTER_BEST
 from .nns_matching import NearestNeighborsMatching
 
 try:  # the real selector, when this package is dropped into a cslam installation
@@ -68,6 +72,7 @@ class LoopClosureSparseMatching(object):
         if lidar:  # reference :22-23,29-30: the ScanContext matcher implements the same three methods
             from .lidar_pr import ScanContextMatching
         make = ScanContextMatching if lidar else NearestNeighborsMatching
+        self._dense = not lidar   # the dense matcher has the batched / multi-database / filtered entries
         self.local_nnsm = make()
         self.other_robots_nnsm = {}
         for i in range(self.params['max_nb_robots']):
@@ -91,14 +96,19 @@ class LoopClosureSparseMatching(object):
         matches = []
         tensor = torch.from_numpy(embedding.astype(np.float32))
         self.local_nnsm.add_item(tensor, keyframe_id)
-        for i in range(self.params['max_nb_robots']):
-            if i != self.params['robot_id']:
-                kf, similarity = self.other_robots_nnsm[i].search_best(tensor)
-                if kf is not None:
-                    if similarity >= self.params['frontend.similarity_threshold']:
-                        match = EdgeInterRobot(self.params['robot_id'], keyframe_id, i, kf, similarity)
-                        self.candidate_selector.add_match(match)
-                        matches.append(match)
+        robots = [i for i in range(self.params['max_nb_robots']) if i != self.params['robot_id']]
+        if self._dense and len(robots) > 1:
+            # f1: the R-1 databases are searched with the query staged once and ONE host synchronisation
+            best = NearestNeighborsMatching.search_best_multi(
+                [self.other_robots_nnsm[i] for i in robots], tensor)
+        else:
+            best = [self.other_robots_nnsm[i].search_best(tensor) for i in robots]
+        for i, (kf, similarity) in zip(robots, best):
+            if kf is not None:
+                if similarity >= self.params['frontend.similarity_threshold']:
+                    match = EdgeInterRobot(self.params['robot_id'], keyframe_id, i, kf, similarity)
+                    self.candidate_selector.add_match(match)
+                    matches.append(match)
         return matches
 
     def add_other_robot_global_descriptor(self, msg):
@@ -133,11 +143,14 @@ class LoopClosureSparseMatching(object):
                                                   [msgs[j].keyframe_id for j in rows])
         if self.local_nnsm.n == 0:
             return [None] * len(msgs)
-        items, sims = self.local_nnsm.search_batch(torch.from_numpy(block), 1)
+        # f2: the `similarity >= threshold` test of :71 runs on the device (FILTER_BEST); pos == 0 <=> passed
+        items, sims, pos = self.local_nnsm.search_candidates(
+            torch.from_numpy(block), 1, mode=FILTER_BEST, batched=True,
+            threshold=self.params['frontend.similarity_threshold'])
         out = []
-        for m, its, s in zip(msgs, items, sims):
+        for m, its, s, p in zip(msgs, items, sims, pos):
             match = None
-            if s[0] >= self.params['frontend.similarity_threshold']:
+            if p == 0:
                 match = EdgeInterRobot(self.params['robot_id'], its[0], m.robot_id, m.keyframe_id, s[0])
                 self.candidate_selector.add_match(match)
             out.append(match)
@@ -146,6 +159,17 @@ class LoopClosureSparseMatching(object):
     def match_local_loop_closures(self, descriptor, kf_id):
         """Reference :78-97 — top `frontend.nb_best_matches` on the local DB, then host filtering."""
         tensor = torch.from_numpy(np.asarray(descriptor).astype(np.float32))
+        nnsm = self.local_nnsm
+        if self._dense and nnsm.n > 0 and nnsm.ids_on_device and isinstance(kf_id, (int, np.integer)):
+            # f2: self-hit drop, min-gap window and threshold are evaluated on the device next to the top-k
+            kfs, similarities, pos = nnsm.search_candidates(
+                tensor, self.params['frontend.nb_best_matches'], query_id=kf_id,
+                min_gap=self.params['frontend.intra_loop_min_inbetween_keyframes'],
+                threshold=self.params['frontend.similarity_threshold'])
+            match = kfs[pos] if pos >= 0 else None
+            if len(kfs) > 0 and kfs[0] == kf_id:
+                similarities = similarities[1:]
+            return match, similarities
         kfs, similarities = self.local_nnsm.search(tensor, k=self.params['frontend.nb_best_matches'])
         if len(kfs) > 0 and kfs[0] == kf_id:
             kfs, similarities = kfs[1:], similarities[1:]

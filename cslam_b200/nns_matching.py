@@ -7,7 +7,9 @@ growable HBM arena owned by ``libcslam_nns.so`` and every search is one hand-wri
 for exposing ``.data`` as a tensor view and for converting inputs exactly like the reference does.
 
 Additive API (does not change any reference signature): ``add_items``, ``search_batch`` and
-``search`` accepting a ``(B, dim)`` query.
+``search`` accepting a ``(B, dim)`` query; ``search_best_multi`` (one query against several databases,
+one synchronisation) and ``search_candidates`` (search + the caller's threshold / self-hit /
+min-gap filter on the device).
 """
 import ctypes
 
@@ -61,6 +63,11 @@ class NearestNeighborsMatching(object):
         self._h = None
         self._view = None
         self._view_key = None
+        # integer identities of the rows, for the device-side candidate filter (search_candidates):
+        # items that are ints are queued here and handed to the library lazily, in one call
+        self._ids_pending = []
+        self._ids_first = 0        # row of _ids_pending[0]
+        self._ids_ok = True        # False once a non-integer item was added
         if dim is not None:
             self._open()
 
@@ -112,6 +119,7 @@ class NearestNeighborsMatching(object):
         row = row.to(torch.float32)
         self._append(h, row)
         self.items[self.n] = item
+        self._note_ids((item,))
         self.n += 1
 
     def add_items(self, matrix, items):
@@ -129,6 +137,7 @@ class NearestNeighborsMatching(object):
         self._append(h, matrix.to(torch.float32))
         for j, item in enumerate(items):
             self.items[self.n + j] = item
+        self._note_ids(items)
         self.n += len(items)
 
     # -- wire / on-disk format (additive) ------------------------------------------------
@@ -237,6 +246,121 @@ class NearestNeighborsMatching(object):
                                     ctypes.c_void_p(sims.ctypes.data), 0, self._stream(), None)
         _native.check(rc, h.h)
         return idx, sims
+
+    # -- device-side candidate filter (additive) ---------------------------------------
+    def _note_ids(self, items):
+        if not self._ids_ok:
+            return
+        for it in items:
+            if isinstance(it, (int, np.integer)) and not isinstance(it, (bool, np.bool_)) \
+                    and -2 ** 63 <= int(it) < 2 ** 63:
+                self._ids_pending.append(int(it))
+            else:  # arbitrary Python objects stay host-only; the filter is then the caller's job
+                self._ids_ok = False
+                self._ids_pending = []
+                return
+
+    @property
+    def ids_on_device(self):
+        """True while every item added so far is an int, i.e. ``search_candidates`` can filter by id."""
+        return self._ids_ok and self._h is not None
+
+    def _flush_ids(self):
+        if self._ids_pending:
+            ids = np.asarray(self._ids_pending, dtype=np.int64)
+            rc = self._h.lib.cslam_nns_set_row_ids(self._h.h, self._ids_first, len(ids),
+                                                   ctypes.c_void_p(ids.ctypes.data))
+            _native.check(rc, self._h.h)
+            self._ids_first += len(ids)
+            self._ids_pending = []
+
+    def search_candidates(self, query, k, query_id=None, min_gap=0, threshold=-np.inf,
+                          mode=_native.FILTER_INTRA, batched=None):
+        """Top-``k`` search plus the candidate filter of the reference's callers, evaluated on the device.
+
+        ``mode=FILTER_INTRA`` (``loop_closure_sparse_matching.py:83-97``): a leading hit whose id equals
+        ``query_id`` is dropped, candidates with ``|id - query_id| < min_gap`` or ``sim < threshold`` are
+        skipped, the first survivor is the match.  ``mode=FILTER_BEST`` (``:51,:71``): the best hit is the
+        match iff ``sim >= threshold``.  ``query`` may be ``(dim,)`` or ``(B, dim)`` (then ``query_id`` is a
+        sequence of B ids or None); ``batched=True`` forces the batch form of the result for B == 1.
+
+        Returns ``(items, sims, pos)``: the UNFILTERED top-k exactly as ``search`` / ``search_batch`` return
+        it, and the position of the accepted candidate in it (-1 = none; an int, or an int32 array of B).
+        """
+        if self._h is None:
+            raise RuntimeError("search_candidates on an empty matcher")
+        if not torch.is_tensor(query):
+            query = torch.from_numpy(np.asarray(query).astype(np.float32))
+        single = not (query.dim() == 2 and not (query.shape[0] == 1 or self.dim == 1))
+        if batched is not None:
+            single = not batched
+        q = (query.reshape(1, self.dim) if single else query.reshape(-1, self.dim))
+        q = q.to(torch.float32).contiguous()
+        B = int(q.shape[0])
+        h = self._h
+        on_dev = q.is_cuda
+        if on_dev and q.device.index != h.lib.cslam_nns_device(h.h):
+            q, on_dev = q.cpu(), False
+        k = int(k)
+        if k < 0:
+            k = max(self.n + k, 0)
+        kk = min(k, self.n)
+        qids = None
+        if query_id is not None:
+            if not self._ids_ok:
+                raise TypeError("search_candidates with query_id needs integer items (keyframe ids)")
+            self._flush_ids()
+            qids = np.ascontiguousarray(np.asarray(query_id, dtype=np.int64).reshape(-1))
+            if len(qids) != B:
+                raise ValueError("need one query_id per query")
+        idx = np.empty((B, max(kk, 1)), dtype=np.int64)
+        sims = np.empty((B, max(kk, 1)), dtype=np.float32)
+        pos = np.full((B,), -1, dtype=np.int32)
+        if kk > 0 and B > 0:
+            thr = np.float32(threshold)   # numpy compares an np.float32 similarity with a python float in fp32
+            rc = h.lib.cslam_nns_search_filtered(
+                h.h, ctypes.c_void_p(q.data_ptr()), B, q.shape[1], 1 if on_dev else 0, kk, int(mode),
+                ctypes.c_void_p(qids.ctypes.data) if qids is not None else None, int(min_gap),
+                ctypes.c_float(float(thr)), ctypes.c_void_p(idx.ctypes.data),
+                ctypes.c_void_p(sims.ctypes.data), ctypes.c_void_p(pos.ctypes.data), self._stream(), None)
+            _native.check(rc, h.h)
+        idx, sims = idx[:, :kk], sims[:, :kk]
+        if single:
+            return [self.items[i] for i in idx[0].tolist()], sims[0], int(pos[0])
+        return [[self.items[i] for i in row] for row in idx.tolist()], sims, pos
+
+    # -- one query, several databases (additive, SURVEY §8 f1) -----------------------------------------
+    @staticmethod
+    def search_best_multi(matchers, query):
+        """``[m.search_best(query) for m in matchers]`` with the query staged once, the kernels of all
+        databases queued back to back and ONE host synchronisation (reference: the per-robot loop of
+        ``loop_closure_sparse_matching.py:47-55``).  Empty matchers give ``(None, None)``."""
+        matchers = list(matchers)
+        live = [m for m in matchers if m._h is not None and m.n > 0]
+        out = [(None, None)] * len(matchers)
+        if not live:
+            for j, m in enumerate(matchers):   # keep the reference's quirks for empty-but-dimensioned DBs
+                out[j] = m.search_best(query)
+            return out
+        m0 = live[0]
+        if not torch.is_tensor(query):
+            query = torch.from_numpy(query.astype(np.float32))
+        q = query.reshape(1, m0.dim).to(torch.float32).contiguous()
+        on_dev = q.is_cuda
+        lib = m0._h.lib
+        if on_dev and q.device.index != lib.cslam_nns_device(m0._h.h):
+            q, on_dev = q.cpu(), False
+        hs = (ctypes.c_void_p * len(live))(*[m._h.h for m in live])
+        idx = np.empty((len(live),), dtype=np.int64)
+        sims = np.empty((len(live),), dtype=np.float32)
+        rc = lib.cslam_nns_search_multi(hs, len(live), ctypes.c_void_p(q.data_ptr()), q.shape[1],
+                                        1 if on_dev else 0, 1, ctypes.c_void_p(idx.ctypes.data),
+                                        ctypes.c_void_p(sims.ctypes.data), None, m0._stream())
+        _native.check(rc, m0._h.h)
+        res = {id(m): (m.items[int(i)], s) for m, i, s in zip(live, idx, sims)}
+        for j, m in enumerate(matchers):
+            out[j] = res[id(m)] if id(m) in res else m.search_best(query)
+        return out
 
     # -- search_best (reference: nns_matching.py:65-78) ----------------------------------------------
     def search_best(self, query):

@@ -94,6 +94,43 @@ int cslam_nns_search(cslam_nns_t h, const float* queries, int64_t B, int64_t q_l
                      int src_is_device, int k, int64_t* out_idx, float* out_sim, int dst_is_device,
                      void* stream, int64_t* out_kk);
 
+/* -- one keyframe against several databases ---------------------------------------- */
+
+/* Replaces the per-robot loop of LoopClosureSparseMatching.add_local_global_descriptor
+ * (loop_closure_sparse_matching.py:47-55): `count` databases (one per other robot) are searched with
+ * the SAME query.  The query is staged once, one single-query kernel per non-empty database is
+ * launched back to back on `stream`, all of them write into one mapped pinned result block, and the
+ * host synchronises ONCE (the reference pays R-1 searches with two host syncs each).
+ * hs[i] may be NULL or empty (kk 0).  All non-empty handles must live on one device and share dim.
+ * query: q_len >= dim fp32 values.  out_idx / out_sim: count x k HOST arrays, entries past kk[i]
+ * filled with -1 / -inf; out_kk (optional): count entries.  Synchronous on return. */
+int cslam_nns_search_multi(const cslam_nns_t* hs, int count, const float* query, int64_t q_len,
+                           int src_is_device, int k, int64_t* out_idx, float* out_sim,
+                           int64_t* out_kk, void* stream);
+
+/* -- candidate filter on the device ----------------------------------------------- */
+
+/* Integer identities (keyframe ids) of rows [first_row, first_row + count): the `item` argument of
+ * add_item when it is an int (nns_matching.py:40; loop_closure_sparse_matching.py:45,65 pass keyframe
+ * ids).  Host-side bookkeeping only; the ids reach the device lazily, as one copy of the not yet
+ * uploaded tail, at the next cslam_nns_search_filtered.  first_row must not leave a gap. */
+int cslam_nns_set_row_ids(cslam_nns_t h, int64_t first_row, int64_t count, const int64_t* ids);
+
+#define CSLAM_NNS_FILTER_BEST 0   /* loop_closure_sparse_matching.py:51,71: best hit iff sim >= threshold */
+#define CSLAM_NNS_FILTER_INTRA 1  /* :83-97: drop a leading self hit, skip |id - query_id| < min_gap,
+                                     skip sim < threshold, first survivor wins */
+/* cslam_nns_search + the caller's candidate filter in one stream-ordered sequence: the top-k goes to
+ * device memory, a filter kernel looks the rows up in the device id table, applies the rule of `mode`
+ * and writes rows, similarities and the position of the accepted candidate (-1 = none) to mapped pinned
+ * memory; one host synchronisation.  query_ids: B host values (the new keyframe's id per query) or NULL
+ * (no self-hit / gap test).  threshold is compared in fp32 like numpy compares an np.float32 with a
+ * python float.  Needs ids for every row (ESTATE otherwise).  out_idx/out_sim: B x k host arrays,
+ * out_match_pos: B host ints.  k <= 128. */
+int cslam_nns_search_filtered(cslam_nns_t h, const float* queries, int64_t B, int64_t q_ld,
+                              int src_is_device, int k, int mode, const int64_t* query_ids,
+                              int64_t min_gap, float threshold, int64_t* out_idx, float* out_sim,
+                              int32_t* out_match_pos, void* stream, int64_t* out_kk);
+
 /* -- row-sharded building blocks (no reference counterpart) -------------------------- */
 
 /* Local top-k of this shard as packed 64-bit keys, written to DEVICE memory out_keys[B*k]

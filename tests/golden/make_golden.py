@@ -147,8 +147,45 @@ def gen_config1():
           "intra matches")
 
 
+def gen_swarm():
+    """4 robots, a real threshold and min-gap window, through the reference's
+    LoopClosureSparseMatching: candidate edges, intra matches and the similarity arrays it returns."""
+    ref_lcsm.NearestNeighborsMatching = lambda *a, **k: ref_matcher()
+    params = {"robot_id": 0, "max_nb_robots": 4, "frontend.sensor_type": "stereo",
+              "frontend.similarity_threshold": 0.85, "frontend.nb_best_matches": 10,
+              "frontend.intra_loop_min_inbetween_keyframes": 20,
+              "frontend.enable_sparsification": True,
+              "evaluation.enable_sparsification_comparison": False}
+    descs = synth.swarm_inputs()
+    n = len(descs[0])
+    lcsm = ref_lcsm.LoopClosureSparseMatching(params, _Node())
+    intra, nsims, first_sim, local_edges = [], [], [], []
+    for i in range(n):
+        ms = lcsm.add_local_global_descriptor(descs[0][i], i)
+        local_edges.append(len(ms))
+        kf, sims = lcsm.match_local_loop_closures(descs[0][i], i)
+        intra.append(-1 if kf is None else kf)
+        nsims.append(len(sims))
+        first_sim.append(sims[0] if len(sims) else np.float32(0))
+        for r in range(1, 4):
+            lcsm.add_other_robot_global_descriptor(GlobalDescriptor(i, r, descs[r][i].tolist()))
+    edges = lcsm.candidate_selector.candidate_edges
+    keys = np.asarray(sorted(edges.keys()), np.int64)
+    weights = np.asarray([edges[tuple(k)].weight for k in keys.tolist()], np.float64)
+    np.savez_compressed(os.path.join(HERE, "swarm_lcsm.npz"), edge_keys=keys, edge_weights=weights,
+                        intra=np.asarray(intra, np.int64), nsims=np.asarray(nsims, np.int64),
+                        first_sim=np.asarray(first_sim, np.float32),
+                        local_edges=np.asarray(local_edges, np.int64))
+    print("swarm_lcsm.npz:", len(keys), "candidate edges;", sum(1 for x in intra if x >= 0),
+          "intra matches;", sum(local_edges), "edges from local keyframes")
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "swarm":
+        gen_swarm()
+        sys.exit(0)
     gen_search_cases()
     gen_edge_cases()
     gen_config1()
+    gen_swarm()

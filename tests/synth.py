@@ -51,6 +51,23 @@ def queries_for(seed, db, nq, dist="rand", every=3, noise=0.05):
     return qs
 
 
+def swarm_inputs(robots=4, n=300, d=64):
+    """4 robots x 300 keyframes x 64-d with planted inter-robot overlaps and intra-robot revisits."""
+    descs = [unit_rows(70 + r, n, d, "rand") for r in range(robots)]
+    eps = normal(79, (robots, n, d)).astype(np.float32)
+    for i in range(100, n, 7):          # robot 0 revisits its own place of 90 keyframes ago
+        v = descs[0][i - 90] + 0.04 * eps[0][i]
+        descs[0][i] = v / np.linalg.norm(v)
+    for i in range(4, n, 9):            # ... and a place of 3 keyframes ago (inside the min-gap window)
+        v = descs[0][i - 3] + 0.04 * eps[0][i]
+        descs[0][i] = v / np.linalg.norm(v)
+    for r in range(1, robots):          # the other robots see places of robot 0
+        for i in range(r, n, 11):
+            v = descs[0][(5 * i + r) % n] + 0.05 * eps[r][i]
+            descs[r][i] = v / np.linalg.norm(v)
+    return descs
+
+
 def scancontexts(seed, n, shape=(20, 60), empty_frac=0.15):
     """(n, rings*sectors) float64 ScanContext-like descriptors: non-negative "max heights" with a share of
     empty bins and a few completely empty sectors (columns), as ptcloud2sc produces for real scans

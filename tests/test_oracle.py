@@ -114,3 +114,24 @@ def test_nan_sorts_first():
     db[2, 0] = np.nan
     idx, _ = oracle.search(db, np.ones(3, np.float32), 2)
     assert idx[0] == 2
+
+
+def test_caller_oracle_matches_reference_swarm_golden(golden_swarm):
+    """oracle/lcsm_oracle.py (the callers' threshold / self-hit / min-gap logic)
+    against the unmodified reference LoopClosureSparseMatching on 4 robots x 300 keyframes."""
+    import synth
+    from conftest import SWARM_PARAMS, check_swarm
+    from oracle.lcsm_oracle import OracleLCSM
+    descs = synth.swarm_inputs()
+    lcsm = OracleLCSM(SWARM_PARAMS)
+    intra, nsims, first, local_edges = [], [], [], []
+    for i in range(len(descs[0])):
+        local_edges.append(len(lcsm.add_local_global_descriptor(descs[0][i], i)))
+        kf, sims = lcsm.match_local_loop_closures(descs[0][i], i)
+        intra.append(-1 if kf is None else kf)
+        nsims.append(len(sims))
+        first.append(sims[0] if len(sims) else 0.0)
+        for r in range(1, 4):
+            lcsm.add_other_robot_global_descriptor(r, i, descs[r][i].tolist())
+    check_swarm(golden_swarm, lcsm.candidate_edges, intra, nsims, first, local_edges)
+    assert sum(1 for x in intra if x >= 0) >= 70 and 400 <= len(lcsm.candidate_edges) <= 460
