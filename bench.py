@@ -316,7 +316,9 @@ def bench_swarm(args):
         return n_match
 
     out = {}
-    for name, fused in (("loop", False), ("multi", True)):
+    for name, fused in (("loop", False), ("multi_serial", True), ("multi", True)):
+        # multi_serial: the same single call, but every kernel waits for the previous one to drain
+        os.environ["CSLAM_NNS_MULTI_OVERLAP"] = "0" if name == "multi_serial" else "1"
         run(fused, 0, args.warmup)
         torch.cuda.synchronize()
         sampler = ClockSampler(0)
@@ -358,6 +360,10 @@ def bench_swarm(args):
             "per_robot_loop": {"value": (R - 1) / out["loop"]["s_per_step"], "unit": "queries/s",
                                "ms_per_step": out["loop"]["s_per_step"] * 1e3,
                                "note": "same kernels through the reference's loop of R-1 synchronised search_best calls"},
+            "multi_without_overlap": {"value": (R - 1) / out["multi_serial"]["s_per_step"], "unit": "queries/s",
+                                      "ms_per_step": out["multi_serial"]["s_per_step"] * 1e3,
+                                      "note": "one call, one synchronisation, but ordinary launches: each database's "
+                                              "kernel starts only after the previous one has drained"},
             "clocks": out["multi"]["clocks"], "gpu_launches": int(out["multi"]["launches"]),
             "matches": out["multi"]["matches"]}
     print(json.dumps(line))

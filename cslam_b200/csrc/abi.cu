@@ -231,7 +231,7 @@ int sync_row_ids(cslam_nns_t h, cudaStream_t stream) {
 // device-accessible out pointers (pitch k_run).  Any of the three outputs may be null.
 int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, int k_run,
                   u64* o_keys, long long* o_idx, float* o_sim, long long idx_stride,
-                  long long idx_offset, cudaStream_t stream) {
+                  long long idx_offset, cudaStream_t stream, bool overlap_prev = false) {
   int variant = h->variant;
   if (variant == 0) {
     if (k_run > kK1MaxK) variant = 3;
@@ -268,6 +268,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       a.idx_stride = idx_stride;
       a.idx_offset = idx_offset;
       a.all_sims = nullptr;
+      a.overlap_prev = overlap_prev && B == 1 && !h->profile;
       KernelTimer kt(h, stream);
       CK(h, k1_launch(a, h->k1, h->num_sms, stream));
     }
@@ -588,11 +589,20 @@ int cslam_nns_search_multi(const cslam_nns_t* hs, int count, const float* query,
   long long* hi = (long long*)h0->res_host.p;
   float* hsim = (float*)(hi + (size_t)count * k);
   std::vector<int> kks(count, 0);
+  cslam_nns_t prev_h = nullptr;
   for (int i = 0; i < count; ++i) {
     cslam_nns_t h = hs[i];
     if (!h || h->dim <= 0 || h->n == 0) continue;
     kks[i] = (int)(k < h->n ? k : h->n);
-    rc = search_device(h, dq, 1, dq_ld, kks[i], nullptr, hi + (size_t)i * k, hsim + (size_t)i * k, 1, 0, stream);
+    // every database after the first may start on the SMs the previous database's kernel has vacated
+    // (programmatic stream serialisation): the searches share the query and nothing else.  Not for a
+    // handle that appears twice (shared scratch) or one whose scratch is still to be set up (a memset
+    // would sit between the two launches anyway).
+    bool overlap = prev_h != nullptr && h->ticket.p != nullptr && env_int("CSLAM_NNS_MULTI_OVERLAP", 1) != 0;
+    for (int j = 0; j < i && overlap; ++j) overlap = hs[j] != h;
+    rc = search_device(h, dq, 1, dq_ld, kks[i], nullptr, hi + (size_t)i * k, hsim + (size_t)i * k, 1, 0, stream,
+                       overlap);
+    prev_h = h;
     if (rc) {
       if (h != h0) h0->err = h->err;
       cudaStreamSynchronize(stream);

@@ -19,6 +19,8 @@
 //   * CTA merge -> scratch[grid][k] -> atomic ticket; the last CTA merges the grid's lists, decodes
 //     and writes the result (optionally straight into mapped pinned host memory).
 #include <cstdlib>
+#include <string.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -84,6 +86,11 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int S = p.stages;
+  // A search of ANOTHER database queued right behind this one with programmatic stream serialisation
+  // (cslam_nns_search_multi: same query, disjoint scratch and outputs, nothing of ours is read by it) may
+  // take over each SM as soon as this grid's CTA there exits, instead of waiting for the whole grid to
+  // drain and a fresh launch.  A no-op when the next launch is an ordinary one.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   unsigned char* stage_base = smem;
   float4* q_s = reinterpret_cast<float4*>(smem + (size_t)W * S * p.stage_bytes);
@@ -569,14 +576,28 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const dim3 g((unsigned)grid), b(W * 32);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = g;
+  cfg.blockDim = b;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  if (a.overlap_prev) {  // see the top of k1_kernel
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  cudaError_t le;
   switch (NQ) {
-    case 4: k1_kernel<4><<<g, b, smem, stream>>>(p); break;
-    case 8: k1_kernel<8><<<g, b, smem, stream>>>(p); break;
-    case 16: k1_kernel<16><<<g, b, smem, stream>>>(p); break;
-    default: k1_kernel<0><<<g, b, smem, stream>>>(p); break;
+    case 4: le = cudaLaunchKernelEx(&cfg, k1_kernel<4>, p); break;
+    case 8: le = cudaLaunchKernelEx(&cfg, k1_kernel<8>, p); break;
+    case 16: le = cudaLaunchKernelEx(&cfg, k1_kernel<16>, p); break;
+    default: le = cudaLaunchKernelEx(&cfg, k1_kernel<0>, p); break;
   }
   count_launch();
-  return cudaGetLastError();
+  return le != cudaSuccess ? le : cudaGetLastError();
 }
 
 }  // namespace cslam

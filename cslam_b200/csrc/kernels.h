@@ -31,6 +31,10 @@ struct K1Args {
   float* out_sim;
   long long idx_stride, idx_offset;
   float* all_sims;  // non-null: write every row's similarity, skip the select
+  // true: launch with programmatic stream serialisation, i.e. this search may start on SMs the PREVIOUS K1
+  // launch in the stream has vacated.  Only valid when the previous launch is a K1 search that shares no
+  // scratch, ticket or output with this one (another database, cslam_nns_search_multi).
+  bool overlap_prev = false;
 };
 
 // Maximum grid K1 will ever use on `device` (sizes the scratch buffer).
