@@ -19,6 +19,20 @@ import torch
 from . import _native
 
 
+def _raw_stream(device_index):
+    """Handle of torch's current CUDA stream on ``device_index`` as an int (the fast private getter that
+    torch's own extensions use, with the public API as the fallback)."""
+    try:
+        return torch._C._cuda_getCurrentRawStream(device_index)
+    except AttributeError:  # pragma: no cover - older/newer torch without the private getter
+        return torch.cuda.current_stream(device_index).cuda_stream
+
+
+def _addr(a):
+    """Address of a numpy array's first element (cheaper than ``a.ctypes.data``)."""
+    return a.__array_interface__['data'][0]
+
+
 class _CudaArrayView:
     """Minimal ``__cuda_array_interface__`` carrier so torch can alias the arena without a copy."""
 
@@ -68,6 +82,7 @@ class NearestNeighborsMatching(object):
         self._ids_pending = []
         self._ids_first = 0        # row of _ids_pending[0]
         self._ids_ok = True        # False once a non-integer item was added
+        self._multi_cache = None   # search_best_multi: (ids of the databases, handle array, result block)
         if dim is not None:
             self._open()
 
@@ -82,11 +97,17 @@ class NearestNeighborsMatching(object):
 
     def _open(self):
         if self._h is None:
-            self._h = _Handle(self._device_index(), self.dim)
+            self._dev_index = self._device_index()
+            self._h = _Handle(self._dev_index, self.dim)
+            # persistent result block of the single-query fast path (k <= 128): the library writes here,
+            # the caller gets copies
+            self._res_idx = np.empty(128, dtype=np.int64)
+            self._res_sim = np.empty(128, dtype=np.float32)
+            self._res_ptr = (_addr(self._res_idx), _addr(self._res_sim))
         return self._h
 
     def _stream(self):
-        return ctypes.c_void_p(torch.cuda.current_stream(self._device_index()).cuda_stream)
+        return ctypes.c_void_p(_raw_stream(self._dev_index if self._h is not None else self._device_index()))
 
     # -- public attribute `data` (reference: nns_matching.py:19-21, read by tests :36,:49,:66) -----
     @property
@@ -115,11 +136,22 @@ class NearestNeighborsMatching(object):
         if self.dim is None:
             self.dim = len(vector)
         h = self._open()
-        row = vector.reshape(1, self.dim)  # RuntimeError on a wrong length, like the reference (:41)
-        row = row.to(torch.float32)
-        self._append(h, row)
+        if (not vector.is_cuda and vector.dtype == torch.float32 and vector.is_contiguous()
+                and vector.numel() == self.dim):
+            # the production call (one CPU fp32 descriptor, reference :45,:64): straight to the C-ABI
+            rc = h.lib.cslam_nns_add(h.h, vector.data_ptr(), 1, self.dim, 0, _raw_stream(self._dev_index), None)
+            if rc:
+                _native.check(rc, h.h)
+        else:
+            row = vector.reshape(1, self.dim)  # RuntimeError on a wrong length, like the reference (:41)
+            row = row.to(torch.float32)
+            self._append(h, row)
         self.items[self.n] = item
-        self._note_ids((item,))
+        if self._ids_ok:
+            if type(item) is int and -0x8000000000000000 <= item <= 0x7fffffffffffffff:
+                self._ids_pending.append(item)
+            else:
+                self._note_ids((item,))
         self.n += 1
 
     def add_items(self, matrix, items):
@@ -185,10 +217,10 @@ class NearestNeighborsMatching(object):
         if on_dev and rows.device.index != h.lib.cslam_nns_device(h.h):
             rows = rows.cpu()
             on_dev = False
-        new_n = ctypes.c_int64()
-        rc = h.lib.cslam_nns_add(h.h, ctypes.c_void_p(rows.data_ptr()), rows.shape[0], rows.shape[1],
-                                 1 if on_dev else 0, self._stream(), ctypes.byref(new_n))
-        _native.check(rc, h.h)
+        rc = h.lib.cslam_nns_add(h.h, rows.data_ptr(), rows.shape[0], rows.shape[1],
+                                 1 if on_dev else 0, _raw_stream(self._dev_index), None)
+        if rc:
+            _native.check(rc, h.h)
 
     # -- search (reference: nns_matching.py:44-63) --------------------------------------------------
     def search(self, query, k):
@@ -203,8 +235,29 @@ class NearestNeighborsMatching(object):
         """
         if self._h is None:  # reference: len(self.data) == 0 -> [], []
             return [], []
+        # Fast path for the production call (one host descriptor, k <= 128): same conversions as the
+        # reference (:57-60), no torch objects in between, results land in a persistent block.
+        dim = self.dim
         if not torch.is_tensor(query):
-            query = torch.from_numpy(query.astype(np.float32))
+            q = query.astype(np.float32)                       # reference :57-58
+            if q.ndim == 2 and not (q.shape[0] == 1 or dim == 1):
+                return self.search_batch(torch.from_numpy(q), k)
+        keep, ptr = self._host_query(query if torch.is_tensor(query) else q)
+        k = int(k)
+        if keep is not None and 0 <= k and min(k, self.n) <= 128:
+            kk = min(k, self.n)
+            if kk == 0:
+                return [], np.empty(0, dtype=np.float32)
+            h = self._h
+            rc = h.lib.cslam_nns_search(h.h, ptr, 1, dim, 0, kk, self._res_ptr[0], self._res_ptr[1], 0,
+                                        _raw_stream(self._dev_index), None)
+            if rc:
+                _native.check(rc, h.h)
+            if kk == 1:
+                return [self.items[int(self._res_idx[0])]], self._res_sim[:1].copy()
+            return [self.items[i] for i in self._res_idx[:kk].tolist()], self._res_sim[:kk].copy()
+        if not torch.is_tensor(query):
+            query = torch.from_numpy(q)
         if query.dim() == 2 and not (query.shape[0] == 1 or self.dim == 1):
             return self.search_batch(query, k)
         out_dtype = np.float64 if query.dtype == torch.float64 else np.float32  # torch promotion
@@ -212,6 +265,22 @@ class NearestNeighborsMatching(object):
         idx, sims = self._search_block(q, k)
         items = [self.items[i] for i in idx[0].tolist()]
         return items, sims[0].astype(out_dtype, copy=False)
+
+    def _host_query(self, query):
+        """``(keepalive, address)`` of ONE host fp32 query of ``dim`` contiguous values, or ``(None, 0)`` when
+        the query needs the general conversion path (device tensor, other dtype, strided).  numpy input must
+        already be float32 (the caller did ``astype``)."""
+        dim = self.dim
+        if not torch.is_tensor(query):
+            if query.size != dim:                               # reference :60 (torch reshape) raises the same
+                raise RuntimeError("shape '[1, %d]' is invalid for input of size %d" % (dim, query.size))
+            if not query.flags.c_contiguous:
+                query = np.ascontiguousarray(query)
+            return query, _addr(query)
+        if (not query.is_cuda and query.dtype == torch.float32 and query.is_contiguous()
+                and query.numel() == dim and query.dim() <= 2):
+            return query, query.data_ptr()
+        return None, 0
 
     def search_batch(self, queries, k):
         """Additive API: ``B`` queries at once -> ``(list of B item lists, sims[B, kk])``."""
@@ -241,10 +310,10 @@ class NearestNeighborsMatching(object):
         if on_dev and q.device.index != h.lib.cslam_nns_device(h.h):
             q = q.cpu()
             on_dev = False
-        rc = h.lib.cslam_nns_search(h.h, ctypes.c_void_p(q.data_ptr()), B, q.shape[1],
-                                    1 if on_dev else 0, kk, ctypes.c_void_p(idx.ctypes.data),
-                                    ctypes.c_void_p(sims.ctypes.data), 0, self._stream(), None)
-        _native.check(rc, h.h)
+        rc = h.lib.cslam_nns_search(h.h, q.data_ptr(), B, q.shape[1], 1 if on_dev else 0, kk,
+                                    _addr(idx), _addr(sims), 0, _raw_stream(self._dev_index), None)
+        if rc:
+            _native.check(rc, h.h)
         return idx, sims
 
     # -- device-side candidate filter (additive) ---------------------------------------
@@ -337,29 +406,40 @@ class NearestNeighborsMatching(object):
         ``loop_closure_sparse_matching.py:47-55``).  Empty matchers give ``(None, None)``."""
         matchers = list(matchers)
         live = [m for m in matchers if m._h is not None and m.n > 0]
-        out = [(None, None)] * len(matchers)
-        if not live:
-            for j, m in enumerate(matchers):   # keep the reference's quirks for empty-but-dimensioned DBs
-                out[j] = m.search_best(query)
-            return out
+        if not live:                        # keep the reference's quirks for empty-but-dimensioned DBs
+            return [m.search_best(query) for m in matchers]
         m0 = live[0]
-        if not torch.is_tensor(query):
-            query = torch.from_numpy(query.astype(np.float32))
-        q = query.reshape(1, m0.dim).to(torch.float32).contiguous()
-        on_dev = q.is_cuda
         lib = m0._h.lib
-        if on_dev and q.device.index != lib.cslam_nns_device(m0._h.h):
-            q, on_dev = q.cpu(), False
-        hs = (ctypes.c_void_p * len(live))(*[m._h.h for m in live])
-        idx = np.empty((len(live),), dtype=np.int64)
-        sims = np.empty((len(live),), dtype=np.float32)
-        rc = lib.cslam_nns_search_multi(hs, len(live), ctypes.c_void_p(q.data_ptr()), q.shape[1],
-                                        1 if on_dev else 0, 1, ctypes.c_void_p(idx.ctypes.data),
-                                        ctypes.c_void_p(sims.ctypes.data), None, m0._stream())
-        _native.check(rc, m0._h.h)
-        res = {id(m): (m.items[int(i)], s) for m, i, s in zip(live, idx, sims)}
-        for j, m in enumerate(matchers):
-            out[j] = res[id(m)] if id(m) in res else m.search_best(query)
+        if not torch.is_tensor(query):
+            query = query.astype(np.float32)                    # reference :57-58
+        keep, ptr = m0._host_query(query)
+        on_dev = 0
+        if keep is None:
+            if not torch.is_tensor(query):
+                query = torch.from_numpy(query)
+            keep = query.reshape(1, m0.dim).to(torch.float32).contiguous()
+            if keep.is_cuda and keep.device.index != lib.cslam_nns_device(m0._h.h):
+                keep = keep.cpu()
+            on_dev, ptr = (1 if keep.is_cuda else 0), keep.data_ptr()
+        key = tuple(map(id, live))
+        cache = m0._multi_cache
+        if cache is None or cache[0] != key:   # the handle array and result block of this set of databases
+            idx = np.empty((len(live),), dtype=np.int64)
+            sims = np.empty((len(live),), dtype=np.float32)
+            cache = m0._multi_cache = (key, (ctypes.c_void_p * len(live))(*[m._h.h for m in live]),
+                                       idx, sims, _addr(idx), _addr(sims))
+        _, hs, idx, sims, p_idx, p_sims = cache
+        rc = lib.cslam_nns_search_multi(hs, len(live), ptr, m0.dim, on_dev, 1, p_idx, p_sims, None,
+                                        _raw_stream(m0._dev_index))
+        if rc:
+            _native.check(rc, m0._h.h)
+        out, j = [], 0
+        for m in matchers:
+            if j < len(live) and live[j] is m:
+                out.append((m.items[int(idx[j])], sims[j]))   # sims[j]: a fresh np.float32 scalar
+                j += 1
+            else:
+                out.append(m.search_best(query))
         return out
 
     # -- search_best (reference: nns_matching.py:65-78) ----------------------------------------------

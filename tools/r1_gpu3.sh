@@ -1,0 +1,14 @@
+#!/bin/bash
+mkdir -p gpurun_out
+B="python bench.py --no-cpu-baseline --no-torch-bar --no-e2e --steps 5"
+for cfg in "0 10" "2 10" "2 32" "2 24" "0 32"; do
+  set -- $cfg
+  echo "== dbg=$1 k=$2" >> gpurun_out/screen_probe.txt
+  CSLAM_NNS_K2_DBG=$1 timeout 200 $B --k $2 2>> gpurun_out/screen_probe.err | python -c "
+import sys, json
+d = json.loads(sys.stdin.read().strip().splitlines()[-1])
+print('ms_per_step %.3f kernel_ms %.3f value %.0f' % (d['ms_per_step'], d['roofline']['kernel_ms'], d['value']))" >> gpurun_out/screen_probe.txt 2>&1
+done
+echo "== prof dbg=2 k=32" >> gpurun_out/screen_probe.txt
+CSLAM_NNS_K2_PROF=1 CSLAM_NNS_K2_DBG=2 timeout 200 $B --k 32 --steps 2 2>&1 | grep "k2q prof" | tail -2 >> gpurun_out/screen_probe.txt
+cat gpurun_out/screen_probe.txt
