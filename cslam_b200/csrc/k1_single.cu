@@ -31,6 +31,19 @@ namespace {
 constexpr int W = kK1Warps;
 constexpr int U = 4;  // rows per lane group per pass
 
+#ifdef K1_PROF
+// Development build only (make K1_PROF=1): per-CTA %globaltimer stamps -> tools/k1_timeline.py
+__device__ unsigned long long g_k1_prof[8 * 512];
+__device__ __forceinline__ void k1_stamp(int slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  g_k1_prof[blockIdx.x * 8 + slot] = t;
+}
+#define K1_STAMP(cond, slot) do { if (cond) k1_stamp(slot); } while (0)
+#else
+#define K1_STAMP(cond, slot) do { } while (0)
+#endif
+
 struct K1Dev {
   const float4* db;
   long long n;
@@ -52,6 +65,7 @@ struct K1Dev {
   long long idx_stride, idx_offset;
   float* all_sims;
   long long keep_rows;  // rows below this are loaded with L2 evict-last, the rest evict-first (0: no hints)
+  long long tiles_div, tiles_rem;  // total tiles / and % (grid * warps): a warp's tile count without a device division
 };
 
 __device__ __forceinline__ void fma4(const float4& x, const float4& q, float& dot, float& nn) {
@@ -91,6 +105,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   // take over each SM as soon as this grid's CTA there exits, instead of waiting for the whole grid to
   // drain and a fresh launch.  A no-op when the next launch is an ordinary one.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  K1_STAMP(tid == 0, 0);  // CTA start
 
   unsigned char* stage_base = smem;
   float4* q_s = reinterpret_cast<float4*>(smem + (size_t)W * S * p.stage_bytes);
@@ -100,11 +115,12 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   float* red = reinterpret_cast<float*>(bars + W * S);
   int* flag = reinterpret_cast<int*>(red + W + 1);
 
+  // tile t of the database belongs to warp t % GW of the grid; the launcher did the 64-bit divisions
+  // (two of them here cost ~0.4 us before the first copy could be issued)
   const long long GW = (long long)gridDim.x * W;
   const long long gw = (long long)blockIdx.x * W + warp;
   const int R = p.rows_per_tile;
-  const long long total_tiles = (p.n + R - 1) / R;
-  const long long my_tiles = gw < total_tiles ? (total_tiles - gw + GW - 1) / GW : 0;
+  const long long my_tiles = p.tiles_div + (gw < p.tiles_rem ? 1 : 0);
   const long long my_items = my_tiles * p.n_chunks;
 
   uint64_t* my_bars = bars + warp * S;
@@ -136,6 +152,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   };
 
   // -- get the first copies in flight before anything else --------------------------------------
+  K1_STAMP(tid == 0, 7);
   if (lane == 0) {
     for (int s = 0; s < S; ++s) mbar_init(&my_bars[s], 1);
     mbar_fence_init();
@@ -147,6 +164,16 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       if (++c == p.n_chunks) { c = 0; ++tj; }
     }
   }
+  K1_STAMP(tid == 0, 4);  // ring primed (mbarrier init + first S bulk copies issued)
+#ifdef K1_PROF
+  if (tid == 1 && my_items > 2) {  // a plain load from a part of the database nobody has touched yet
+    const float4* far = p.db + ((gw + 2 * GW) * p.rows_per_tile) * p.ld4 + 8;
+    float4 v;
+    asm volatile("ld.global.cv.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(far));
+    if (v.x == 123456.f) g_k1_prof[0] = 0;  // keep the dependency
+    k1_stamp(6);
+  }
+#endif
   // position of the NEXT item to issue (item index it + S while consuming item it)
   long long nx_tile = p.n_chunks == 1 ? (long long)S : (long long)(S / p.n_chunks);
   int nx_chunk = p.n_chunks == 1 ? 0 : S % p.n_chunks;
@@ -184,6 +211,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     }
     part = group_sum(part, lpr);
     const float inv_qn = 1.0f / fmaxf(sqrtf(part), kEps);
+    K1_STAMP(tid == 0 && inv_qn != 123456.f, 5);  // query in registers
 
     int s = 0;
     uint32_t parity = 0;
@@ -192,6 +220,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       const long long rows_ll = p.n - row0;
       const int rows = rows_ll > R ? R : (int)rows_ll;
       mbar_wait(&my_bars[s], parity);
+      K1_STAMP(tid == 0 && it == 0, 1);  // first bytes have landed
       const float4* buf = reinterpret_cast<const float4*>(my_stage + (size_t)s * p.stage_bytes);
       for (int r0 = 0; r0 < rows; r0 += G) {
         const int rr = r0 + grp;
@@ -291,6 +320,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     }
   }
   if (p.all_sims) return;
+  K1_STAMP(tid == 0, 2);  // warp 0 of this CTA is through its share of the stream
 
   // -- k == 1: the best key of the grid is one atomicMax per CTA; the CTA that draws the last ticket
   //    decodes and publishes it.  No scratch lists, no second merge level. ------------------------------
@@ -305,6 +335,7 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
       if (best != 0ull) atomicMax(gbest, best);
       __threadfence();
       const unsigned t = atomicAdd(p.ticket, 1u);
+      K1_STAMP(true, 3);  // ticket drawn
       if (t == gridDim.x - 1) {
         __threadfence();
         const u64 key = atomicExch(gbest, 0ull);
@@ -486,6 +517,12 @@ inline int ceil_log2(int v) {
 
 }  // namespace
 
+#ifdef K1_PROF
+extern "C" __attribute__((visibility("default"))) int cslam_k1_prof_read(unsigned long long* out, int ctas) {
+  return (int)cudaMemcpyFromSymbol(out, g_k1_prof, sizeof(unsigned long long) * 8 * ctas);
+}
+#endif
+
 int k1_max_grid(int num_sms) { return num_sms > 0 ? num_sms * 2 : 296; }
 
 cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStream_t stream) {
@@ -563,6 +600,8 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   while (grid > 1 && (size_t)grid * (a.k + 1) * 8 > (size_t)W * p.stages * p.stage_bytes) --grid;
   if ((size_t)grid * (a.k + 1) * 8 > (size_t)W * p.stages * p.stage_bytes) return cudaErrorInvalidConfiguration;
   const size_t smem = (size_t)W * p.stages * p.stage_bytes + fixed;
+  p.tiles_div = tiles / (grid * W);
+  p.tiles_rem = tiles % (grid * W);
   static bool attr_set[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
