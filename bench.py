@@ -446,9 +446,23 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # BASELINE configs[3] (c4): "incremental add_item between queries" — every step first appends one new
+    # descriptor (device-resident leg: a stream-ordered device-to-device row copy; end-to-end leg: the
+    # public add_item with a host row), then searches.  The database grows by one row per step.
+    incremental = args.workload == "c4" and world == 1
+    extra = None
+    if incremental:
+        extra = torch.rand((64, dim), generator=gq, device=dev, dtype=torch.float32)
+        extra /= extra.norm(dim=1, keepdim=True)
+
+    def device_step(i):
+        if incremental:
+            m.add_local_shard(extra[i % 64:i % 64 + 1])
+        m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+
     # ---- device-resident leg: `value` + roofline -----------------------------------------------------
     for i in range(args.warmup):
-        m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+        device_step(i)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -457,7 +471,7 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
-        m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+        device_step(i)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -478,7 +492,7 @@ def main():
         sampler.start()
         time.sleep(0.1)
         for i in range(reps):
-            m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+            device_step(i)
         barrier()
         clocks = sampler.stop()
         clocks["sampled"] = "%d untimed repeats of the step right after the timed region" % reps
@@ -492,7 +506,11 @@ def main():
     if not args.no_e2e:
         hq = [torch.from_numpy(q.cpu().numpy()).pin_memory() for q in qb]
 
+        extra_host = extra.cpu() if incremental else None
+
         def e2e_step(q_host):
+            if incremental:  # the reference's add_item: one host row, item = its row number
+                m.local.add_item(extra_host[m.local.n % 64], m.local.n)
             if world == 1:   # host queries in, host (rows, sims) out through cslam_nns_search
                 return m.local._search_block(q_host, k)
             q_dev = q_host.to(dev, non_blocking=True)
@@ -511,7 +529,8 @@ def main():
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": args.steps * batch / float(t.item()), "unit": "queries/s",
-               "h2d_bytes_per_step": batch * dim * 4, "d2h_bytes_per_step": batch * k * 12}
+               "h2d_bytes_per_step": batch * dim * 4 + (dim * 4 if incremental else 0),
+               "d2h_bytes_per_step": batch * k * 12}
 
     # ---- the reference's own GPU arithmetic on the same box (informational bar, SURVEY §8 d3 iii) ------
     torch_bar = None
@@ -573,6 +592,8 @@ def main():
             "scaling": "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products, fp32 accumulate)"
             if variant == 2 else "f32", "data": "synthetic",
             "config": dict(workload_config(args, rows, dim, batch, k), search_variant=variant,
+                           **({"step": "1 add_item (one new row) + 1 search; the database grows by one row per step"}
+                              if incremental else {}),
                            **({"exchange": "K5 peer-memory kernel (csrc/k5_exchange.cu)"
                                if getattr(m, "_xchg", None) is not None else "NCCL all-gather + K4"} if world > 1 else {})),
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches)}
