@@ -69,6 +69,8 @@ XCHG_SIGNATURES = {
     "cslam_nns_xchg_merge": (_c.c_int, [_handle, _c.c_void_p, _i64, _c.c_int, _c.c_int, _c.c_void_p,
                                         _c.c_void_p, _c.c_void_p]),
     "cslam_nns_xchg_status": (_c.c_int, [_handle]),
+    "cslam_nns_search_sharded": (_c.c_int, [_handle, _handle, _f32p, _i64, _i64, _c.c_int, _c.c_int, _c.c_int,
+                                            _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_void_p]),
 }
 
 SC_SIGNATURES = {

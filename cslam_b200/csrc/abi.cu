@@ -89,7 +89,7 @@ struct cslam_nns_s {
   int variant = 0, last_variant = 0;
   K1Tuning k1;
   // device scratch
-  DevBuf q, q_lo, inv_qn, scratch, ticket, part_keys, res_dev, all_sims, sort_tmp, sort_kv, qids;
+  DevBuf q, q_lo, inv_qn, scratch, ticket, part_keys, res_dev, all_sims, sort_tmp, sort_kv, qids, shard_keys;
   PinBuf res_host;
   // integer row identities for the device-side candidate filter (cslam_nns_search_filtered)
   Arena ids_arena;
@@ -427,7 +427,7 @@ int cslam_nns_destroy(cslam_nns_t h) {
     cudaDeviceSynchronize();
     h->arena.release();
     h->ids_arena.release();
-    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket, &h->qids,
+    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket, &h->qids, &h->shard_keys,
                       &h->part_keys, &h->res_dev, &h->all_sims, &h->sort_tmp, &h->sort_kv};
     for (DevBuf* b : bufs) b->free();
     h->res_host.free();
@@ -708,6 +708,29 @@ int cslam_nns_search_keys(cslam_nns_t h, const float* queries, int64_t B, int64_
   if (rc) return rc;
   return search_device(h, dq, B, dq_ld, k, (u64*)out_keys_dev, nullptr, nullptr, row_stride,
                        row_offset, stream);
+}
+
+int cslam_nns_search_sharded(cslam_nns_t h, cslam_nns_xchg_t x, const float* queries, int64_t B, int64_t q_ld,
+                             int src_is_device, int k, int rank, int world, int phase, int64_t* out_idx_dev,
+                             float* out_sim_dev, void* stream_) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  if (!x || B <= 0 || k <= 0 || world < 1 || rank < 0 || rank >= world || phase < 1 || phase > 3)
+    return fail(h, CSLAM_NNS_EINVAL, "bad arguments to cslam_nns_search_sharded");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  DeviceGuard g(h->device);
+  if (!h->shard_keys.ensure((size_t)B * k * 8)) return fail(h, CSLAM_NNS_ENOMEM, "shard key buffer");
+  uint64_t* keys = (uint64_t*)h->shard_keys.p;
+  if (phase & 1) {
+    if (h->dim <= 0 || h->n == 0) {  // this rank owns no row yet
+      CK(h, cudaMemsetAsync(keys, 0, (size_t)B * k * 8, stream));
+    } else {
+      int rc = cslam_nns_search_keys(h, queries, B, q_ld, src_is_device, k, world, rank, keys, stream_);
+      if (rc) return rc;
+    }
+  }
+  int rc = cslam_nns_xchg_merge(x, keys, B, k, phase, out_idx_dev, out_sim_dev, stream_);
+  if (rc) return fail(h, rc, std::string("exchange: ") + cslam_nns_xchg_last_error(x));
+  return 0;
 }
 
 int cslam_nns_merge_keys(int device, const uint64_t* keys_dev, int parts, int64_t B, int k,

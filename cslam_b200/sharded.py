@@ -182,19 +182,21 @@ class ShardedNearestNeighborsMatching(object):
                                         1, self.local._stream(), None)
             _native.check(rc, h.h)
             return out_idx, out_sim
-        keys = self.search_keys_device(q_dev, k)
         if out_idx is None:
             out_idx = torch.empty((B, k), dtype=torch.int64, device=q_dev.device)
             out_sim = torch.empty((B, k), dtype=torch.float32, device=q_dev.device)
         xchg = self._exchange(q_dev.device) if (k <= 32 and B <= 4096 and B * k <= 131072) else None
         if xchg is not None:
-            lib = _native.load()
-            rc = lib.cslam_nns_xchg_merge(xchg, ctypes.c_void_p(keys.data_ptr()), B, k, 3,
-                                          ctypes.c_void_p(out_idx.data_ptr()), ctypes.c_void_p(out_sim.data_ptr()),
-                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
-            if rc != _native.OK:
-                raise _native.NativeError(rc, lib.cslam_nns_xchg_last_error(xchg).decode("utf-8", "replace"))
+            # local search + exchange + merge in ONE C-ABI call (cslam_nns_search_sharded)
+            if self.local.dim is None and self.dim is not None:
+                self.local.dim = self.dim  # this rank owns no row yet
+            h = self.local._open()
+            rc = h.lib.cslam_nns_search_sharded(h.h, xchg, q_dev.data_ptr(), B, q_dev.shape[1], 1, k, self.rank,
+                                                self.world, 3, out_idx.data_ptr(), out_sim.data_ptr(),
+                                                self.local._stream())
+            _native.check(rc, h.h)
             return out_idx, out_sim
+        keys = self.search_keys_device(q_dev, k)
         if self.world > 1:
             gathered = torch.empty((self.world, B, k), dtype=torch.int64, device=q_dev.device)
             dist.all_gather_into_tensor(gathered, keys, group=self.group)

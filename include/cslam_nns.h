@@ -176,6 +176,19 @@ int cslam_nns_xchg_merge(cslam_nns_xchg_t x, const uint64_t* local_keys_dev, int
 /* 0, or CSLAM_NNS_ECUDA when an earlier call timed out waiting for a peer (read after a stream sync). */
 int cslam_nns_xchg_status(cslam_nns_xchg_t x);
 
+/* This rank's part of ONE row-sharded search in a single call (SURVEY §8 b2 / e): the local top-k of shard `h`
+ * as packed keys carrying the GLOBAL row (local_row * world + rank, the striped layout), then the exchange +
+ * merge kernel over peer memory.  Equivalent to cslam_nns_search_keys into an internal buffer followed by
+ * cslam_nns_xchg_merge; every rank makes the same call with the same queries.  Outputs are DEVICE arrays
+ * [B][k] (global rows, similarities; -1 / -inf past the end), identical on every rank and bit-identical to an
+ * unsharded search of the concatenated database.  Stream-ordered, no host synchronisation.  `h` may hold an
+ * empty shard.  phase as in cslam_nns_xchg_merge: 3 in production; 1 = search + push, 2 = wait + merge (tests).
+ * Limits of the exchange kernel apply (k <= 32, B <= 4096); beyond them use cslam_nns_search_keys, an
+ * all-gather of the keys (NCCL) and cslam_nns_merge_keys. */
+int cslam_nns_search_sharded(cslam_nns_t h, cslam_nns_xchg_t x, const float* queries, int64_t B, int64_t q_ld,
+                             int src_is_device, int k, int rank, int world, int phase,
+                             int64_t* out_idx_dev, float* out_sim_dev, void* stream);
+
 /* -- tuning / diagnostics ----------------------------------------------------------------------- */
 
 /* Force a search variant for tests and profiling: 0 = automatic, 1 = single-query kernel looped,

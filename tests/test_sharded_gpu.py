@@ -155,3 +155,60 @@ def test_peer_exchange_timeout_is_an_error_not_a_hang(monkeypatch):
     finally:
         for r in range(2):
             lib.cslam_nns_xchg_destroy(xs[r])
+
+
+@pytest.mark.parametrize("world,n,d,B,k", [(2, 4001, 256, 32, 10), (4, 3000, 100, 1, 1), (3, 2, 64, 5, 10)])
+def test_search_sharded_single_call_equals_unsharded(world, n, d, B, k):
+    """cslam_nns_search_sharded (local search + exchange + merge in ONE C-ABI call) with one GPU
+    playing every rank: phase 1 (search + push) on every rank, then phase 2 (wait + merge) on every rank.
+    Every rank must end with the unsharded search's rows and bit-identical similarities; a rank without rows
+    (n < world) takes part with an empty shard."""
+    import synth
+    from cslam_b200 import _native, nns_matching as M
+    lib = _native.load()
+    db = synth.unit_rows(61, n, d, "rand")
+    qs = synth.queries_for(62, db, B, "rand")
+    q_dev = torch.from_numpy(qs).cuda()
+    whole = M.NearestNeighborsMatching(dim=d)
+    whole.add_items(torch.from_numpy(db), list(range(n)))
+    widx, wsims = whole._search_block(q_dev, k)
+    kk = widx.shape[1]
+    shards = []
+    for r in range(world):
+        m = M.NearestNeighborsMatching(dim=d)
+        if len(db[r::world]):
+            m.add_items(torch.from_numpy(db[r::world]), list(range(len(db[r::world]))))
+        shards.append(m)
+    xs = (ctypes.c_void_p * world)()
+    for r in range(world):
+        x = ctypes.c_void_p()
+        assert lib.cslam_nns_xchg_create(0, world, r, ctypes.byref(x)) == 0, lib.cslam_nns_xchg_last_error(None)
+        xs[r] = x
+    try:
+        for r in range(world):
+            assert lib.cslam_nns_xchg_connect_local(xs[r], xs) == 0
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        outs = []
+        for phase in (1, 2):
+            for r in range(world):
+                idx = torch.full((B, k), -7, dtype=torch.int64, device="cuda")
+                sim = torch.full((B, k), 7.0, dtype=torch.float32, device="cuda")
+                h = shards[r]._h
+                rc = lib.cslam_nns_search_sharded(h.h, xs[r], q_dev.data_ptr(), B, d, 1, k, r, world, phase,
+                                                  idx.data_ptr(), sim.data_ptr(), stream)
+                _native.check(rc, h.h)
+                if phase == 2:
+                    outs.append((idx, sim))
+        torch.cuda.synchronize()
+        for r, (idx, sim) in enumerate(outs):
+            assert lib.cslam_nns_xchg_status(xs[r]) == 0
+            assert np.array_equal(idx.cpu().numpy()[:, :kk], widx), r
+            assert np.array_equal(sim.cpu().numpy()[:, :kk], wsims), r
+            assert (idx.cpu().numpy()[:, kk:] == -1).all()
+        h = shards[0]._h
+        assert lib.cslam_nns_search_sharded(h.h, xs[0], q_dev.data_ptr(), B, d, 1, k, world, world, 3,
+                                            None, None, stream) == _native.EINVAL     # rank out of range
+    finally:
+        torch.cuda.synchronize()
+        for r in range(world):
+            lib.cslam_nns_xchg_destroy(xs[r])
