@@ -89,3 +89,42 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.lower().replace("test infrastructure", ""), f
+
+
+def test_host_query_fast_path_rules():
+    """Which queries may take the no-torch fast path of search / search_best_multi (host fp32, contiguous,
+    exactly dim values) and that a wrong length raises RuntimeError like the reference's torch reshape
+    (cslam/nns_matching.py:60)."""
+    from cslam_b200 import NearestNeighborsMatching as M
+    m = M()
+    m.dim = 8
+    q = np.arange(8, dtype=np.float32)
+    keep, ptr = m._host_query(q)
+    assert keep is q and ptr == q.ctypes.data
+    strided = np.arange(16, dtype=np.float32)[::2]
+    keep, ptr = m._host_query(strided)
+    assert keep.flags.c_contiguous and np.array_equal(keep, strided) and ptr == keep.ctypes.data
+    with pytest.raises(RuntimeError):
+        m._host_query(np.zeros(7, np.float32))
+    t = torch.arange(8, dtype=torch.float32)
+    assert m._host_query(t) == (t, t.data_ptr()) or m._host_query(t)[1] == t.data_ptr()
+    assert m._host_query(t.reshape(1, 8))[1] == t.data_ptr()
+    assert m._host_query(t.double()) == (None, 0)              # float64 torch query: promotion path
+    assert m._host_query(torch.arange(16, dtype=torch.float32)[::2]) == (None, 0)   # strided
+    assert m._host_query(torch.zeros(7)) == (None, 0)          # wrong length: the general path raises
+
+
+def test_integer_item_tracking_for_the_device_filter():
+    """ids reach the device id table only while EVERY item is an int (keyframe ids); bools, strings and
+    out-of-range ints switch the table off for good (search_candidates then refuses an id filter)."""
+    from cslam_b200 import NearestNeighborsMatching as M
+    m = M()
+    m._note_ids([1, np.int64(2), np.int32(-3)])
+    assert m._ids_ok and m._ids_pending == [1, 2, -3]
+    m._note_ids([2 ** 63])
+    assert not m._ids_ok and m._ids_pending == []
+    for bad in (True, "kf", 1.5, None, (1, 2)):
+        m2 = M()
+        m2._note_ids([7, bad])
+        assert not m2._ids_ok and m2._ids_pending == []
+    assert not M().ids_on_device        # nothing allocated yet
