@@ -145,6 +145,22 @@ __device__ __forceinline__ void offer(u64* list, int k, u64 key, bool have, u64&
   }
 }
 
+// Top 32 of the union of two descending lists held one key per lane (0 = empty).  C[i] = max(A[i], B[31 - i])
+// is a bitonic sequence that holds exactly the 32 largest keys of the union; five compare-exchange stages
+// sort it descending.  ~12 shuffles whatever the lists hold, against ~200 clk for EVERY key the one-at-a-time
+// insertion of offer() accepts: this is what the merge steps of the k <= 32 tails use.
+__device__ __forceinline__ u64 warp_merge_desc(u64 a, u64 b, int lane) {
+  const u64 br = __shfl_sync(kFull, b, 31 - lane);
+  u64 v = a > br ? a : br;
+#pragma unroll
+  for (int j = 16; j > 0; j >>= 1) {
+    const u64 o = __shfl_xor_sync(kFull, v, j);
+    const bool want_max = (lane & j) == 0;  // the lower lane of a pair keeps the larger key
+    v = (want_max == (v > o)) ? v : o;
+  }
+  return v;
+}
+
 // Block-wide exact select: out[r] = the candidate with exactly r larger candidates, for r < k.
 // Keys are unique (they embed the row) except for empties (0), which are skipped.  `out[0..k)` must be
 // zeroed and visible to the block before the call; all threads of the block call it.  O(M^2 / threads)

@@ -350,27 +350,23 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     return;
   }
 
-  // -- 2 <= k <= 32: register lists all the way.  Warp 0 folds the CTA's 8 warp lists into its own and
-  //    publishes them; in the CTA that draws the last ticket every warp folds 1/8 of the grid's lists
-  //    (loads batched 4 deep so the L2 round trips overlap), warp 0 folds those 8 and writes the result. ----
+  // -- 2 <= k <= 32: register lists all the way, merged with bitonic networks (warp_merge_desc): warp 0
+  //    merges the CTA's 8 warp lists and publishes the result; in the CTA that draws the last ticket every
+  //    warp merges 1/8 of the grid's CTA lists (loads batched 4 lists deep so the L2 round trips overlap),
+  //    warp 0 merges those 8 and writes the result.  A merge costs the same ~12 shuffles whatever the lists
+  //    hold (the one-key-at-a-time insertion this replaced cost ~200 clk per accepted key, ~30 of them per
+  //    level: k = 10 at 100k x 512 took 14 us longer than k = 1). ------------------------------------------
   if (p.k <= 32) {
-    if (lane < p.k) my_list[lane] = mine;
+    const int k = p.k;
+    if (lane < k) my_list[lane] = mine;
     __syncthreads();
     if (warp == 0) {
-      // floor: the best k-th key of any warp list (k keys at or above it exist, so nothing below it
-      // can be in the CTA's top-k)
-      u64 fl = lane < W ? lists[(size_t)lane * p.k + (p.k - 1)] : 0ull;
+      u64 o[W - 1];
 #pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        const u64 o = __shfl_xor_sync(kFull, fl, off);
-        fl = o > fl ? o : fl;
-      }
-      for (int base = p.k; base < W * p.k; base += 32) {
-        const int i = base + lane;
-        const u64 key = i < W * p.k ? lists[i] : 0ull;
-        offer(my_list, p.k, key, key != 0ull, thr, mine, lane, fl);
-      }
-      if (lane < p.k) p.scratch[(size_t)blockIdx.x * p.k + lane] = mine;
+      for (int w = 1; w < W; ++w) o[w - 1] = lane < k ? lists[(size_t)w * k + lane] : 0ull;
+#pragma unroll
+      for (int w = 1; w < W; ++w) mine = warp_merge_desc(mine, o[w - 1], lane);
+      if (lane < k) p.scratch[(size_t)blockIdx.x * k + lane] = mine;
       __threadfence();
       __syncwarp();
       unsigned t = 0;
@@ -381,44 +377,29 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     __syncthreads();
     if (!*flag) return;
     __threadfence();
-    const int total = (int)gridDim.x * p.k;
-    const int per_warp = (total + W - 1) / W;
-    const int lo = warp * per_warp;
-    const int hi = lo + per_warp < total ? lo + per_warp : total;
-    thr = 0ull;
+    // CTA lists warp, warp + W, ... of the grid
     mine = 0ull;
-    // floor: the best k-th key of any CTA list (every warp computes it; the loads are L2 hits in flight
-    // together with the first batch below)
-    u64 gfl = 0ull;
-    for (int c = lane; c < (int)gridDim.x; c += 32) {
-      const u64 v = __ldcg(p.scratch + (size_t)c * p.k + (p.k - 1));
-      gfl = v > gfl ? v : gfl;
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-      const u64 o = __shfl_xor_sync(kFull, gfl, off);
-      gfl = o > gfl ? o : gfl;
-    }
-    for (int base = lo; base < hi; base += 128) {
-      u64 kk[4];
+    const int G_ = (int)gridDim.x;
+    for (int c0 = warp; c0 < G_; c0 += 4 * W) {
+      u64 o[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int i = base + u * 32 + lane;
-        kk[u] = i < hi ? __ldcg(p.scratch + i) : 0ull;
+        const int c = c0 + u * W;
+        o[u] = (c < G_ && lane < k) ? __ldcg(p.scratch + (size_t)c * k + lane) : 0ull;
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) offer(my_list, p.k, kk[u], kk[u] != 0ull, thr, mine, lane, gfl);
+      for (int u = 0; u < 4; ++u) mine = warp_merge_desc(mine, o[u], lane);
     }
     __syncthreads();  // everybody is past reading `lists` as the CTA merge's input
-    if (lane < p.k) my_list[lane] = mine;
+    if (lane < k) my_list[lane] = mine;
     __syncthreads();
     if (warp == 0) {
-      for (int base = p.k; base < W * p.k; base += 32) {
-        const int i = base + lane;
-        const u64 key = i < W * p.k ? lists[i] : 0ull;
-        offer(my_list, p.k, key, key != 0ull, thr, mine, lane, gfl);
-      }
-      if (lane < p.k) {
+      u64 o[W - 1];
+#pragma unroll
+      for (int w = 1; w < W; ++w) o[w - 1] = lane < k ? lists[(size_t)w * k + lane] : 0ull;
+#pragma unroll
+      for (int w = 1; w < W; ++w) mine = warp_merge_desc(mine, o[w - 1], lane);
+      if (lane < k) {
         const u64 key = mine;
         const bool have = key != 0ull;
         const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
