@@ -104,6 +104,9 @@ class NearestNeighborsMatching(object):
             self._res_idx = np.empty(128, dtype=np.int64)
             self._res_sim = np.empty(128, dtype=np.float32)
             self._res_ptr = (_addr(self._res_idx), _addr(self._res_sim))
+            self._qid_buf = np.zeros(1, dtype=np.int64)
+            self._pos_buf = np.zeros(1, dtype=np.int32)
+            self._qid_ptr, self._pos_ptr = _addr(self._qid_buf), _addr(self._pos_buf)
         return self._h
 
     def _stream(self):
@@ -363,6 +366,27 @@ class NearestNeighborsMatching(object):
         single = not (query.dim() == 2 and not (query.shape[0] == 1 or self.dim == 1))
         if batched is not None:
             single = not batched
+        if single and 0 < int(k) and min(int(k), self.n) <= 128:
+            # the per-keyframe call (one host descriptor): no torch objects, persistent result block
+            keep, ptr = self._host_query(query)
+            if keep is not None:
+                kk = min(int(k), self.n)
+                qid = None
+                if query_id is not None:
+                    if not self._ids_ok:
+                        raise TypeError("search_candidates with query_id needs integer items (keyframe ids)")
+                    self._flush_ids()
+                    qid = self._qid_buf
+                    qid[0] = query_id
+                h = self._h
+                rc = h.lib.cslam_nns_search_filtered(
+                    h.h, ptr, 1, self.dim, 0, kk, int(mode), self._qid_ptr if qid is not None else None,
+                    int(min_gap), float(np.float32(threshold)), self._res_ptr[0], self._res_ptr[1],
+                    self._pos_ptr, _raw_stream(self._dev_index), None)
+                if rc:
+                    _native.check(rc, h.h)
+                return ([self.items[i] for i in self._res_idx[:kk].tolist()], self._res_sim[:kk].copy(),
+                        int(self._pos_buf[0]))
         q = (query.reshape(1, self.dim) if single else query.reshape(-1, self.dim))
         q = q.to(torch.float32).contiguous()
         B = int(q.shape[0])
