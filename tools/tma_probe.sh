@@ -1,4 +1,5 @@
 #!/bin/bash
+# build first: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/tma_probe tools/tma_probe.cu -lcuda
 P=tools/tma_probe
 # bk rows panels S hot ctas ld iters W gdesc
 for hot in 1 0; do
