@@ -366,10 +366,12 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             nn = fmaf(x[i].x, x[i].x, nn); nn = fmaf(x[i].y, x[i].y, nn);
             nn = fmaf(x[i].z, x[i].z, nn); nn = fmaf(x[i].w, x[i].w, nn);
             sx += (x[i].x + x[i].y) + (x[i].z + x[i].w);
-            if (!(p.dbg & 8)) raw[c] = h;
-            lo[c] = l;
+            if (!(p.dbg & 16)) {  // dbg 16 (with dbg 2): read-only converter, the probe of a screening pass
+              if (!(p.dbg & 8)) raw[c] = h;
+              lo[c] = l;
+            }
           }
-          fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+          if (!(p.dbg & 16)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
         }
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(&conv_bar[s], 0);
