@@ -1,22 +1,31 @@
 #!/usr/bin/env python
 """Headline benchmark: NN-search queries/s on the configuration BASELINE.json's metric is quoted on.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|c4|c5|swarm|sc]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload c3|c2|c2_k10|c4|c5|swarm|sc] [--no-legs]
 
-Default workload ``c3`` = BASELINE.json configs[2]: 1M x 4096 fp32 descriptors, batches of 256
-queries, top-10 (the "1M x 4096 DB" the metric names).  One *step* = one batch of 256 queries
-searched against the whole database.  With N > 1 ranks (torchrun) the SAME database is row-striped
-over the ranks (strong scaling), every step ends with one all-gather of the B*k packed keys and
-the merge kernel, and timing is the max over ranks of a CUDA-event interval.
+Primary workload ``c3`` = BASELINE.json configs[2]: 1M x 4096 fp32 descriptors, batches of 256 queries,
+top-10 (the "1M x 4096 DB" the metric names).  One *step* = one batch of 256 queries searched against the
+whole database.  With N > 1 ranks (torchrun) the SAME database is row-striped over the ranks (strong
+scaling), every step ends with one exchange of the B*k packed keys fused with the merge, and timing is the
+max over ranks of a CUDA-event interval.
 
-The line printed by rank 0 carries, besides the base contract: ``roofline`` (dominant kernel,
-timed live with CUDA events around that kernel only), ``cpu_baseline`` (the C oracle port on the
-host cores, bounded sample), ``e2e`` (same metric through the public Python API with HOST buffers),
-``clocks`` and ``gpu_launches``.
+Without ``--workload`` the line also carries ``legs``: short runs of the other BASELINE configurations, each
+with its own ``roofline``, ``e2e``, ``clocks``, ``parity`` and ``gpu_reference`` —
 
-``--impl reference`` times the reference's CPU path for the same metric: the reference is Python +
-torch (cslam/nns_matching.py) and /root/reference does not exist on the benchmark box, so this arm
-runs the oracle port (oracle/nns_oracle.c, one pthread per core) — see DESIGN.md.
+    N == 1 : c2 (100k x 512, search_best), c2_k10 (same database, search k=10), c4 (2M x 256, add_item between
+             searches), swarm (configs[3] as 8 robots through LoopClosureSparseMatching), c5 (10M x 256, B=256)
+    N  > 1 : c5 (10M x 256 row-striped over the N ranks: the scaling sweep BASELINE configs[4] names)
+
+Every workload ends with a PARITY GATE outside any timing (``parity``): a subsample of the queries of the last
+steps is searched again by the reference's own three torch calls (cslam/nns_matching.py:61-63, restated in
+tests/refops.py) on the SAME resident database view, every rank scoring its own shard, and the library's
+rows / similarities must satisfy BASELINE.md §5's rule; a violation makes the process exit non-zero.
+
+``--impl reference`` times the reference's CPU path for the same metric: the reference is Python + torch
+(cslam/nns_matching.py) and /root/reference does not exist on the benchmark box, so this arm runs the
+reference's own three torch calls on CPU tensors (all host threads) and, beside it, the C oracle port
+(oracle/nns_oracle.c, one pthread per core), both on a bounded row sample — see DESIGN.md §7.
 """
 import argparse
 import ctypes
@@ -34,10 +43,13 @@ WORKLOADS = {
     # name: (rows, dim, batch, k, description)
     "c3": (1_000_000, 4096, 256, 10, "BASELINE configs[2]: NetVLAD-shaped 1M x 4096 fp32, batch 256, top-10"),
     "c2": (100_000, 512, 1, 1, "BASELINE configs[1]: CosPlace-shaped 100k x 512 fp32, single query, top-1"),
+    "c2_k10": (100_000, 512, 1, 10, "BASELINE configs[1]'s database, single query, top-10 (the intra-robot "
+                                   "search of loop_closure_sparse_matching.py:80-81)"),
     "c4": (2_000_000, 256, 1, 1, "BASELINE configs[3]: 2M x 256 fp32, add_item between single-query top-1 searches"),
     "c5": (10_000_000, 256, 256, 10, "BASELINE configs[4]: 10M x 256 fp32 row-sharded, batch 256, top-10"),
 }
 METRIC = "NN-search queries/s at 1M×4096 DB; achieved HBM GB/s and fraction of roofline"
+HBM_NOMINAL_GBS = 8000.0   # the "roughly 8 TB/s peak" BASELINE.json's north_star states its target against
 
 
 def parse():
@@ -46,7 +58,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + ["sc", "swarm"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS) + ["sc", "swarm"])
+    ap.add_argument("--no-legs", action="store_true", help="primary workload only")
     ap.add_argument("--robots", type=int, default=8, help="swarm workload: number of robots R")
     ap.add_argument("--rows", type=int, default=0, help="override the row count (debugging only)")
     ap.add_argument("--dim", type=int, default=0, help="override the descriptor size (debugging only)")
@@ -54,14 +67,26 @@ def parse():
     ap.add_argument("--k", type=int, default=0, help="override k (debugging only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-torch-bar", action="store_true",
-                    help="skip the stock torch-on-CUDA restatement of the reference's search (N=1 only)")
+                    help="skip the stock torch-on-CUDA restatement of the reference's search (gpu_reference)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity gate (debugging only)")
+    ap.add_argument("--parity-queries", type=int, default=32)
     return ap.parse_args()
 
 
 # -------------------------------------------------------------------------------------------------
-# CPU arm (oracle port) — used by cpu_baseline and by --impl reference
+# CPU arms — used by cpu_baseline and by --impl reference
 # -------------------------------------------------------------------------------------------------
+
+def _cpu_sample(rows, dim, nq, seed=3):
+    import numpy as np
+    sample_rows = min(rows, max(1024, (256 << 20) // (dim * 4)))      # <= 256 MB of descriptors
+    rng = np.random.default_rng(seed)
+    db = rng.random((sample_rows, dim), dtype=np.float32)
+    db /= np.linalg.norm(db, axis=1, keepdims=True)
+    qs = rng.random((nq, dim), dtype=np.float32)
+    return sample_rows, db, qs
+
 
 def cpu_port_qps(rows, dim, batch, k, budget_s=12.0):
     """Time the C oracle on a bounded row sample of the workload; returns (queries/s scaled to the
@@ -78,12 +103,8 @@ def cpu_port_qps(rows, dim, batch, k, budget_s=12.0):
                                   ctypes.c_void_p]
     lib.oracle_num_threads.restype = ctypes.c_int
     cores = lib.oracle_num_threads()
-    sample_rows = min(rows, max(1024, (256 << 20) // (dim * 4)))      # <= 256 MB of descriptors
-    rng = np.random.default_rng(3)
-    db = rng.random((sample_rows, dim), dtype=np.float32)
-    db /= np.linalg.norm(db, axis=1, keepdims=True)
     nq = batch
-    qs = rng.random((nq, dim), dtype=np.float32)
+    sample_rows, db, qs = _cpu_sample(rows, dim, nq)
     idx = np.empty((nq, k), np.int64)
     sims = np.empty((nq, k), np.float32)
 
@@ -102,6 +123,48 @@ def cpu_port_qps(rows, dim, batch, k, budget_s=12.0):
     desc = ("%d of %d queries over a %d-row sample (1/%.0f of the rows, cost scaled linearly in rows); "
             "C port of nns_matching.py:57-63, %d pthreads" % (nrun, nq, sample_rows, scale, cores))
     return qps_sample / scale, cores, desc
+
+
+def cpu_torch_qps(rows, dim, batch, k, budget_s=12.0):
+    """The reference's OWN arithmetic on the host: the three torch calls of cslam/nns_matching.py:61-63 on CPU
+    tensors (what the reference class executes with its device forced to CPU), one query at a time like the
+    reference's API, all intra-op threads torch has.  Bounded row sample, cost scaled linearly in rows."""
+    import torch
+    sample_rows, db, qs = _cpu_sample(rows, dim, min(batch, 64))
+    view = torch.from_numpy(db)
+    tq = torch.from_numpy(qs)
+
+    def one(j):
+        q = tq[j % len(tq)].reshape(1, dim)
+        sim = torch.nn.functional.cosine_similarity(view, q)                 # :61
+        ns = torch.argsort(sim, descending=True)[:k]                         # :62
+        return ns.tolist(), torch.gather(sim, 0, ns).cpu().numpy()           # :63
+
+    one(0)
+    t0 = time.perf_counter()
+    one(1)
+    t1 = max(time.perf_counter() - t0, 1e-6)
+    nrun = int(max(2, min(256, budget_s / t1)))
+    t0 = time.perf_counter()
+    for j in range(nrun):
+        one(j)
+    t = time.perf_counter() - t0
+    scale = rows / sample_rows
+    threads = torch.get_num_threads()
+    desc = ("%d single-query searches over a %d-row sample (1/%.0f of the rows, cost scaled linearly in rows); the "
+            "reference's own torch calls (cosine_similarity + argsort + gather, nns_matching.py:61-63) on CPU "
+            "tensors, torch %s, %d intra-op threads, os.cpu_count()=%s"
+            % (nrun, sample_rows, scale, torch.__version__, threads, os.cpu_count()))
+    return nrun / t / scale, threads, desc
+
+
+def cpu_baseline_block(rows, dim, batch, k, budget_s):
+    """cpu_baseline object: the reference's torch-CPU arithmetic (value) with the C port beside it."""
+    v, threads, desc = cpu_torch_qps(rows, dim, batch, k, budget_s * 0.5)
+    pv, cores, pdesc = cpu_port_qps(rows, dim, batch, k, budget_s * 0.5)
+    return {"value": v, "unit": "queries/s", "cores": threads, "kind": "port", "sample": desc,
+            "extrapolated": True,
+            "c_port": {"value": pv, "unit": "queries/s", "cores": cores, "sample": pdesc}}
 
 
 # -------------------------------------------------------------------------------------------------
@@ -146,20 +209,20 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons)}
 
 
-def torch_cuda_bar(view, q_block, k):
+def gpu_reference_bar(view, q_block, k, nq=20):
     """The reference's search arithmetic (cslam/nns_matching.py:57-63: cosine_similarity over the stored
     rows, full argsort, gather, two device->host reads) restated with stock torch ops on the SAME device and
     the same resident database (the zero-copy `.data` view), one query at a time as the reference's API is.
     /root/reference itself cannot travel to the benchmark box; this is PyTorch library code used as a bar,
-    never part of the product path.  A few queries are timed and the rate is per query."""
+    never part of the product path."""
     import torch
 
     def one(q):
         sim = torch.nn.functional.cosine_similarity(view, q.view(1, -1))
         order = torch.argsort(sim, descending=True)[:k]
-        return order.cpu().numpy(), sim[order].cpu().numpy()
+        return order.tolist(), torch.gather(sim, 0, order).cpu().numpy()
 
-    nq, nb_ = 4, int(q_block.shape[0])
+    nb_ = int(q_block.shape[0])
     try:
         one(q_block[0])
         torch.cuda.synchronize()
@@ -173,8 +236,9 @@ def torch_cuda_bar(view, q_block, k):
     finally:
         torch.cuda.empty_cache()
     return {"value": 1.0 / dt, "unit": "queries/s", "kind": "port",
-            "sample": "%d single-query searches (torch %s: cosine_similarity + argsort + gather + 2 D2H reads), "
-                      "same device, same resident database" % (nq, torch.__version__)}
+            "sample": "%d single-query searches (torch %s: cosine_similarity + argsort + gather + 2 D2H reads, the "
+                      "reference's nns_matching.py:61-63), same B200, same resident database"
+                      % (nq, torch.__version__)}
 
 
 def measured_peaks():
@@ -185,32 +249,91 @@ def measured_peaks():
         return 6650.0, 1590.0, 1400.0, "fallback"
 
 
+_TF32_PEAK = None
+
+
+def measure_tf32_peak(dev):
+    """cuBLAS TF32 dense matmul on this GPU in this run (torch.matmul 8192^3 with allow_tf32, outside every
+    timed region): best of 10 (burst) and a ~1.5 s back-to-back loop (sustained, under the power cap) — the
+    denominator of the batched kernel's tensor roofline, instead of assuming bf16 / 2."""
+    global _TF32_PEAK
+    if _TF32_PEAK is not None:
+        return _TF32_PEAK
+    import torch
+    try:
+        old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = True
+        n = 8192
+        a = torch.randn((n, n), device=dev, dtype=torch.float32)
+        b = torch.randn((n, n), device=dev, dtype=torch.float32)
+        c = torch.empty((n, n), device=dev, dtype=torch.float32)
+        for _ in range(3):
+            torch.matmul(a, b, out=c)
+        torch.cuda.synchronize()
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch.matmul(a, b, out=c)
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        reps = int(max(10, 1500.0 / best))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            torch.matmul(a, b, out=c)
+        e1.record()
+        e1.synchronize()
+        sust = e0.elapsed_time(e1) / reps
+        torch.backends.cuda.matmul.allow_tf32 = old
+        del a, b, c
+        torch.cuda.empty_cache()
+        fl = 2.0 * n ** 3 / 1e12
+        _TF32_PEAK = {"burst": fl / (best / 1e3), "sustained": fl / (sust / 1e3),
+                      "how": "torch.matmul fp32 8192^3 with allow_tf32 (cuBLAS tf32 tensor-core GEMM) on this GPU in "
+                             "this run: best of 10 and %d back to back" % reps}
+    except Exception as e:  # pragma: no cover
+        _TF32_PEAK = {"burst": None, "sustained": None, "how": "failed: %s" % str(e)[:80]}
+    return _TF32_PEAK
+
+
 # -------------------------------------------------------------------------------------------------
-def reference_arm(args, rows, dim, batch, k):
+def reference_arm(args, name, rows, dim, batch, k):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    vals = []
-    desc, cores = "", 1
+    vals, pvals = [], []
+    desc, pdesc, threads, cores = "", "", 1, 1
+    per = max(2.0, 60.0 / max(1, args.steps + args.warmup))
     for i in range(args.warmup + args.steps):
-        qps, cores, desc = cpu_port_qps(rows, dim, batch, k, budget_s=max(2.0, 60.0 / max(1, args.steps + args.warmup)))
+        qps, threads, desc = cpu_torch_qps(rows, dim, batch, k, budget_s=per * 0.6)
+        pq, cores, pdesc = cpu_port_qps(rows, dim, batch, k, budget_s=per * 0.4)
         if i >= args.warmup:
             vals.append(qps)
+            pvals.append(pq)
     v = sum(vals) / len(vals)
+    pv = sum(pvals) / len(pvals)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "queries/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": batch / v * 1e3,
+            "extrapolated": True,
+            "extrapolation": "each step times a bounded sample of the workload on the host (rows and queries as "
+                             "stated in cpu_baseline.sample) and scales linearly in rows; ms_per_step is the "
+                             "extrapolated cost of one full %d-query step, not the time this process ran" % batch,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args, rows, dim, batch, k),
-            "cpu_baseline": {"value": v, "unit": "queries/s", "cores": cores, "kind": "port", "sample": desc},
+            "data": "synthetic", "config": workload_config(name, args.gpus, rows, dim, batch, k),
+            "cpu_baseline": {"value": v, "unit": "queries/s", "cores": threads, "kind": "port", "sample": desc,
+                             "extrapolated": True,
+                             "c_port": {"value": pv, "unit": "queries/s", "cores": cores, "sample": pdesc}},
             "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
-def workload_config(args, rows, dim, batch, k):
-    return {"workload": WORKLOADS[args.workload][4], "rows": rows, "dim": dim, "batch": batch, "k": k,
-            "sharding": "row-striped over %d rank(s), one exchange of B*k keys per rank per step" % args.gpus
-            if args.gpus > 1 else "single GPU",
-            "l2": "database (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (rows * dim * 4 / 1e9)}
+def workload_config(name, gpus, rows, dim, batch, k):
+    return {"workload": WORKLOADS[name][4], "rows": rows, "dim": dim, "batch": batch, "k": k,
+            "sharding": "row-striped over %d rank(s), one exchange of B*k keys per rank per step" % gpus
+            if gpus > 1 else "single GPU",
+            "l2": "database (%.2f GB) is far larger than the 126 MB L2; no flush needed" % (rows * dim * 4 / 1e9)}
 
 
 def bench_scancontext(args):
@@ -228,7 +351,6 @@ def bench_scancontext(args):
     lib = _native.load()
     base = synth.scancontexts(61, 2000)
     m = ScanContextMatching()
-    rng = np.random.default_rng(7)
     for i in range(n):   # distinct descriptors: a base scan, rolled and scaled
         m.add_item(np.roll(base[i % 2000].reshape(20, 60), i // 2000, axis=1) * (1.0 + 1e-3 * (i // 2000)), i)
     qs = synth.sc_queries_for(1061, base, 64)
@@ -270,16 +392,19 @@ def bench_scancontext(args):
     print(json.dumps(line))
 
 
-def bench_swarm(args):
+def run_swarm(args, steps, warmup, cpu_budget=12.0):
     """SURVEY §8 d1 C4 in its swarm form + f1/f2: R robots (default 8), the 2M x 256 database of BASELINE
     configs[3] split into R per-robot databases of 2M/R rows.  One step = one local keyframe through the
     drop-in ``LoopClosureSparseMatching.add_local_global_descriptor`` (1 add_item on the local database +
     R-1 search_best on the other robots' databases, threshold test, edge bookkeeping) — host descriptor in,
-    host matches out, so the whole leg is end to end.  Timed twice on the same object: through
-    ``search_best_multi`` (one staging, R-1 kernels back to back, ONE synchronisation; the default) and
-    through the reference's per-robot loop (R-1 synchronised searches)."""
+    host matches out, so the whole leg is end to end.  Timed three times on the same object: through
+    ``search_best_multi`` (one staging, R-1 kernels back to back, ONE synchronisation; the default), the same
+    without the launch overlap, and through the reference's per-robot loop (R-1 synchronised searches).
+    Parity: the (keyframe, similarity) every robot's database returns for a subsample of the descriptors is
+    checked against the reference's torch ops on that database's view."""
     import numpy as np
     import torch
+    import refops
     from cslam_b200 import _native
     from cslam_b200.loop_closure_sparse_matching import CandidateEdges, LoopClosureSparseMatching
     torch.cuda.set_device(0)
@@ -302,7 +427,7 @@ def bench_swarm(args):
         if r == 1:
             probe = x[:4096].cpu().numpy()
         del x
-    nq = args.warmup + args.steps
+    nq = warmup + steps
     rng = np.random.default_rng(5)
     qs = rng.random((nq, dim)).astype(np.float32)
     qs[::4] = probe[: len(qs[::4])] + 0.02 * rng.standard_normal((len(qs[::4]), dim)).astype(np.float32)
@@ -319,29 +444,52 @@ def bench_swarm(args):
     for name, fused in (("loop", False), ("multi_serial", True), ("multi", True)):
         # multi_serial: the same single call, but every kernel waits for the previous one to drain
         os.environ["CSLAM_NNS_MULTI_OVERLAP"] = "0" if name == "multi_serial" else "1"
-        run(fused, 0, args.warmup)
+        run(fused, 0, warmup)
         torch.cuda.synchronize()
         sampler = ClockSampler(0)
         sampler.start()
         l0 = lib.cslam_nns_launch_count()
         t0 = time.perf_counter()
-        nm = run(fused, args.warmup, nq)
+        nm = run(fused, warmup, nq)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
-        out[name] = {"s_per_step": dt / args.steps, "matches": nm, "launches": lib.cslam_nns_launch_count() - l0,
+        out[name] = {"s_per_step": dt / steps, "matches": nm, "launches": lib.cslam_nns_launch_count() - l0,
                      "clocks": sampler.stop()}
     assert out["loop"]["matches"] == out["multi"]["matches"]
     lcsm._dense = True
+    # parity gate: search_best_multi's answers for a subsample of the descriptors, per robot database
+    parity = None
+    if not args.no_parity:
+        from cslam_b200 import NearestNeighborsMatching
+        robots = [i for i in range(R) if i != 0]
+        sub = list(range(0, nq, max(1, nq // min(args.parity_queries, nq))))[:args.parity_queries]
+        res = [NearestNeighborsMatching.search_best_multi([lcsm.other_robots_nnsm[i] for i in robots], qs[j])
+               for j in sub]
+        qd = torch.from_numpy(qs[sub]).to(dev)
+        rep = None
+        for a, i in enumerate(robots):
+            mch = lcsm.other_robots_nnsm[i]
+            rows_ = np.asarray([[res[b][a][0]] for b in range(len(sub))], np.int64)
+            sims_ = np.asarray([[res[b][a][1]] for b in range(len(sub))], np.float32)
+            r_ = refops.check_against_reference(mch.data[:mch.n], qd, 1, rows_, sims_)
+            if rep is None:
+                rep = r_
+            else:
+                for f in ("queries", "non_tie", "ties", "bad_sims", "bad_fp64"):
+                    setattr(rep, f, getattr(rep, f) + getattr(r_, f))
+                rep.max_rel, rep.max_abs64 = max(rep.max_rel, r_.max_rel), max(rep.max_abs64, r_.max_abs64)
+                rep.first = rep.first or r_.first
+        parity = rep.as_dict()
+        parity["queries"] = "%d descriptors x %d robot databases" % (len(sub), len(robots))
     hbm_peak, _, _, which = measured_peaks()
     dt = out["multi"]["s_per_step"]
     bytes_ = float(R - 1) * per * dim * 4
     cpu = None
     if not args.no_cpu_baseline:
-        v, cores, desc = cpu_port_qps(per, dim, 1, 1)
-        cpu = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port", "sample": desc}
+        cpu = cpu_baseline_block(per, dim, 1, 1, cpu_budget)
     qps = (R - 1) / dt
-    line = {"metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": 1, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+    line = {"metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": 1, "steps": steps,
+            "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "BASELINE configs[3] as a swarm: %d robots, %d x %d fp32 per robot database, one "
                                    "step = add_local_global_descriptor (1 add_item + %d search_best + threshold)"
@@ -350,7 +498,8 @@ def bench_swarm(args):
                        "l2": "the %d databases searched per step total %.2f GB, far larger than the 126 MB L2; no "
                              "flush needed" % (R - 1, bytes_ / 1e9)},
             "roofline": {"bound": "hbm", "achieved": bytes_ / dt / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": bytes_ / dt / 1e9 / hbm_peak, "traffic": None, "kernel": "k1_single_query",
+                         "frac": bytes_ / dt / 1e9 / hbm_peak, "frac_nominal_8tbs": bytes_ / dt / 1e9 / HBM_NOMINAL_GBS,
+                         "traffic": None, "kernel": "k1_single_query",
                          "note": "END-TO-END figure: (R-1) * rows * ld * 4 algorithmic bytes per step / wall time of "
                                  "the whole Python call (H2D of the row and the query, R-1 kernels, one sync, edge "
                                  "bookkeeping); peak = %s copy bandwidth" % which},
@@ -365,46 +514,56 @@ def bench_swarm(args):
                                       "note": "one call, one synchronisation, but ordinary launches: each database's "
                                               "kernel starts only after the previous one has drained"},
             "clocks": out["multi"]["clocks"], "gpu_launches": int(out["multi"]["launches"]),
-            "matches": out["multi"]["matches"]}
-    print(json.dumps(line))
+            "matches": out["multi"]["matches"], "parity": parity}
+    del lcsm
+    torch.cuda.empty_cache()
+    return line
 
 
-def main():
-    args = parse()
-    if args.workload == "sc":
-        return bench_scancontext(args)
-    if args.workload == "swarm":
-        if args.impl == "reference":   # the CPU arm of one per-robot database: BASELINE configs[3]'s shape
-            args.workload = "c4"
-            return reference_arm(args, (args.rows or 2_000_000) // args.robots, args.dim or 256, 1, 1)
-        return bench_swarm(args)
-    rows, dim, batch, k, _ = WORKLOADS[args.workload]
-    if args.rows:
-        rows = args.rows
-    if args.dim:
-        dim = args.dim
-    if args.batch:
-        batch = args.batch
-    if args.k:
-        k = args.k
-    if args.impl == "reference":
-        return reference_arm(args, rows, dim, batch, k)
+class Ctx(object):
+    """Process-wide state of one bench run (device, ranks, library)."""
 
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        from cslam_b200 import _native
+        self.args = args
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        assert self.world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
+        self.lib = _native.load()
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+
+def run_dense(ctx, name, rows, dim, batch, k, steps, warmup, cpu_budget=12.0, overridden=False):
+    """One dense-matcher workload on ctx.world ranks; returns the line dict on rank 0 (None elsewhere) and
+    whether the parity gate passed (identical on every rank)."""
     import numpy as np
     import torch
     import torch.distributed as dist
-    from cslam_b200 import _native
+    import refops
     from cslam_b200.sharded import ShardedNearestNeighborsMatching
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
-    lib = _native.load()
+    args, world, rank, dev, lib = ctx.args, ctx.world, ctx.rank, ctx.dev, ctx.lib
+    single = batch == 1
 
     # ---- synthetic database: this rank's stripe, generated on the device in chunks ------------------
     m = ShardedNearestNeighborsMatching(dim=dim)
@@ -419,7 +578,7 @@ def main():
         x = torch.rand((c, dim), generator=gen, device=dev, dtype=torch.float32)
         x /= x.norm(dim=1, keepdim=True)
         if probe is None:
-            probe = x[: 4 * batch].clone()
+            probe = x[: max(4 * batch, 64)].clone()
         m.add_local_shard(x)
         done += c
         del x
@@ -428,7 +587,7 @@ def main():
     # queries: same on every rank; every 10th is a noisy copy of a rank-0 row (true neighbours exist)
     gq = torch.Generator(device=dev)
     gq.manual_seed(4)
-    nb = 4
+    nb = 4 if not single else 64
     queries = torch.rand((nb * batch, dim), generator=gq, device=dev, dtype=torch.float32)
     if probe.shape[0] >= queries.shape[0]:
         queries[::10] = probe[: queries.shape[0]][::10] + 0.02 * torch.randn(
@@ -441,15 +600,10 @@ def main():
     out_sim = torch.empty((batch, k), dtype=torch.float32, device=dev)
     h = m.local._h
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     # BASELINE configs[3] (c4): "incremental add_item between queries" — every step first appends one new
     # descriptor (device-resident leg: a stream-ordered device-to-device row copy; end-to-end leg: the
     # public add_item with a host row), then searches.  The database grows by one row per step.
-    incremental = args.workload == "c4" and world == 1
+    incremental = name == "c4" and world == 1
     extra = None
     if incremental:
         extra = torch.rand((64, dim), generator=gq, device=dev, dtype=torch.float32)
@@ -461,86 +615,142 @@ def main():
         m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
 
     # ---- device-resident leg: `value` + roofline -----------------------------------------------------
-    for i in range(args.warmup):
+    for i in range(warmup):
         device_step(i)
-    barrier()
-    sampler = ClockSampler(local_rank)
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local_rank)
     sampler.start()
     lib.cslam_nns_profile(h.h, 1)
     launches0 = lib.cslam_nns_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(args.steps):
+    for i in range(steps):
         device_step(i)
     e1.record()
-    barrier()
+    ctx.barrier()
     ms = e0.elapsed_time(e1)
     launches = lib.cslam_nns_launch_count() - launches0
     kms, kl = ctypes.c_float(), ctypes.c_int64()
     lib.cslam_nns_profile_read(h.h, ctypes.byref(kms), ctypes.byref(kl))
     lib.cslam_nns_profile(h.h, 0)
     clocks = sampler.stop()
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    ms = ctx.max_over_ranks(ms)
     if clocks["sm_mhz"] is None:
         # the timed region was shorter than one NVML poll (50 ms): repeat the same step for ~0.5 s right
         # after it, outside any timing, only to read the clocks under this load (same count on every rank)
-        reps = int(min(200000, max(8, 0.5 / max(ms / 1e3 / args.steps, 1e-6))))
-        sampler = ClockSampler(local_rank)
+        reps = int(min(200000, max(8, 0.5 / max(ms / 1e3 / steps, 1e-6))))
+        sampler = ClockSampler(ctx.local_rank)
         sampler.start()
         time.sleep(0.1)
         for i in range(reps):
             device_step(i)
-        barrier()
+        ctx.barrier()
         clocks = sampler.stop()
         clocks["sampled"] = "%d untimed repeats of the step right after the timed region" % reps
     else:
         clocks["sampled"] = "during the timed region"
-    value = args.steps * batch / (ms / 1e3)
+    value = steps * batch / (ms / 1e3)
     variant = lib.cslam_nns_last_variant(h.h)
+    screen = None
+    if hasattr(lib, "cslam_nns_screen_stats"):
+        a_, b_ = ctypes.c_int64(), ctypes.c_int64()
+        lib.cslam_nns_screen_stats(h.h, ctypes.byref(a_), ctypes.byref(b_))
+        if a_.value:
+            screen = {"queries_screened": int(a_.value), "queries_fallback": int(b_.value),
+                      "fallback_rate": b_.value / max(1, a_.value)}
+
+    # ---- results of the last timed step, kept for the parity gate ------------------------------------
+    if single:
+        par_q = queries[: min(args.parity_queries, queries.shape[0])].contiguous()
+        par_idx = torch.empty((par_q.shape[0], k), dtype=torch.int64, device=dev)
+        par_sim = torch.empty((par_q.shape[0], k), dtype=torch.float32, device=dev)
+        for j in range(par_q.shape[0]):
+            m.search_batch_device(par_q[j:j + 1], k, par_idx[j:j + 1], par_sim[j:j + 1])
+    else:
+        last = (steps - 1) % nb
+        npar = min(args.parity_queries, batch)
+        par_q = qb[last][:npar].contiguous()
+        par_idx, par_sim = out_idx[:npar].clone(), out_sim[:npar].clone()
+    torch.cuda.synchronize()
 
     # ---- end-to-end leg: public Python API, host buffers --------------------------------------------
     e2e = None
     if not args.no_e2e:
+        if world == 1:   # the drop-in's items dict: row -> keyframe id (an int, as in production); the 10M-row
+            # database gets the storage-free identity mapping instead of a 10M-entry dict
+            from cslam_b200.sharded import RowIdentity
+            m.local.items = dict(zip(range(rows + steps + 8), range(rows + steps + 8))) \
+                if rows <= 4_000_000 else RowIdentity()
         hq = [torch.from_numpy(q.cpu().numpy()).pin_memory() for q in qb]
-
+        hq_np = [q.numpy() for q in hq]
         extra_host = extra.cpu() if incremental else None
 
-        def e2e_step(q_host):
-            if incremental:  # the reference's add_item: one host row, item = its row number
+        def e2e_step(i):
+            if world > 1:     # every rank uploads 1/world of the block, one all-gather, results to rank 0 only
+                return m.search_batch(hq[i % nb], k, root_only=True)
+            if incremental:   # the reference's add_item: one host row, item = its row number
                 m.local.add_item(extra_host[m.local.n % 64], m.local.n)
-            if world == 1:   # host queries in, host (rows, sims) out through cslam_nns_search
-                return m.local._search_block(q_host, k)
-            q_dev = q_host.to(dev, non_blocking=True)
-            i_dev, s_dev = m.search_batch_device(q_dev, k)
-            return i_dev.cpu(), s_dev.cpu()
+            if not single:    # host queries in, host (items, sims) out through the public batched call
+                return m.local.search_batch(hq[i % nb], k)
+            if k == 1:        # the reference's signature: numpy descriptor in, (item, np.float32) out
+                return m.local.search_best(hq_np[i % nb][0])
+            return m.local.search(hq_np[i % nb][0], k)
 
-        for i in range(min(args.warmup, 2)):
-            e2e_step(hq[i % nb])
-        barrier()
+        for i in range(min(warmup, 3)):
+            e2e_step(i)
+        ctx.barrier()
         t0 = time.perf_counter()
-        for i in range(args.steps):
-            e2e_step(hq[i % nb])
+        for i in range(steps):
+            e2e_step(i)
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
-        t = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": args.steps * batch / float(t.item()), "unit": "queries/s",
+        dt = ctx.max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": steps * batch / dt, "unit": "queries/s", "ms_per_step": dt / steps * 1e3,
                "h2d_bytes_per_step": batch * dim * 4 + (dim * 4 if incremental else 0),
-               "d2h_bytes_per_step": batch * k * 12}
+               "d2h_bytes_per_step": batch * k * 12,
+               "api": ("ShardedNearestNeighborsMatching.search_batch(host queries, k, root_only=True): each rank "
+                       "uploads 1/%d of the block, one all-gather over NVLink, rank 0 alone reads the results"
+                       % world) if world > 1 else
+                      ("NearestNeighborsMatching.search_batch(host queries, k) -> (items, sims)" if not single else
+                       ("add_item(host row) + " if incremental else "") +
+                       ("search_best(numpy descriptor)" if k == 1 else "search(numpy descriptor, k)"))}
 
-    # ---- the reference's own GPU arithmetic on the same box (informational bar, SURVEY §8 d3 iii) ------
-    torch_bar = None
-    if world == 1 and not args.no_torch_bar:
-        torch_bar = torch_cuda_bar(m.local.data[:m.local.n], qb[0], k)
-
-    if rank != 0:
+    # ---- parity gate (outside any timing) ------------------------------------------------------------
+    parity, ok = None, True
+    if not args.no_parity:
+        view = m.local.data[:m.local.n]
+        rep = refops.check_against_reference(view, par_q, k, par_idx, par_sim, rank, world)
+        parity = rep.as_dict()
+        ok = rep.ok
         if world > 1:
-            dist.destroy_process_group()
-        return
+            # the NCCL all-gather + K4 route must return the same bits as the peer-memory kernel
+            i2, s2 = m.search_batch_device(par_q, k, exchange="nccl")
+            i1, s1 = m.search_batch_device(par_q, k)
+            torch.cuda.synchronize()
+            same = bool(torch.equal(i1, i2) and torch.equal(s1, s2) and torch.equal(i1, par_idx)
+                        and torch.equal(s1, par_sim))
+            flag = torch.tensor([1 if same else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            parity["peer_route_equals_nccl_route_bitwise"] = bool(int(flag.item()))
+            parity["ok"] = parity["ok"] and parity["peer_route_equals_nccl_route_bitwise"]
+            ok = parity["ok"]
+
+    # ---- the reference's own GPU arithmetic on the same box (SURVEY §8 d3 iii) -----------------------
+    gpu_ref = None
+    if world == 1 and not args.no_torch_bar:
+        gpu_ref = gpu_reference_bar(m.local.data[:m.local.n], qb[0] if not single else queries, k)
+
+    tf32 = measure_tf32_peak(dev) if (variant == 2 and rank == 0) else None
+    b2b = None
+    if variant != 2 and rank == 0:
+        # the same kernel timed as 200 back-to-back launches inside the library (no Python between launches)
+        b2b = ctypes.c_float()
+        lib.cslam_nns_time_search(h.h, ctypes.c_void_p(qb[0].data_ptr()), batch, dim, k, 200,
+                                  ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), ctypes.byref(b2b))
+    xchg_peer = getattr(m, "_xchg", None) is not None
+    del m, h
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None, ok
 
     # ---- roofline of the dominant kernel --------------------------------------------------------------
     hbm_peak, tf_burst, tf_sust, which = measured_peaks()
@@ -550,31 +760,42 @@ def main():
         per_launch_q = min(batch, 256)
         flops = 2.0 * local_rows * dim * per_launch_q
         achieved = flops / (k_ms / 1e3) / 1e12
-        peak = tf_sust / 2.0
+        if tf32 and tf32["sustained"]:
+            peak, peak_note = tf32["sustained"], "cuBLAS tf32 GEMM measured in this run, sustained (%s)" % tf32["how"]
+        else:
+            peak, peak_note = tf_sust / 2.0, "%s bf16 sustained %.0f TF/s / 2" % (which, tf_sust)
+        bytes_ = float(local_rows) * ((dim + 3) // 4 * 4) * 4
         roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                "frac": achieved / peak, "traffic": None, "kernel": "k2_tcgen05_3xtf32",
-                "issued_frac": 3.0 * achieved / peak, "kernel_ms": k_ms, "launches": kl.value,
-                "note": "achieved = algorithmic 2*N*D*B flops per launch / CUDA-event duration; peak = "
-                        "%s bf16 sustained %.0f TF/s / 2 (tf32 dense is half the bf16 rate); issued_frac "
-                        "counts the 3 tf32 products of the 3xTF32 split" % (which, tf_sust)}
+                "frac": achieved / peak, "traffic": None, "kernel": "k2_tcgen05",
+                "kernel_ms": k_ms, "launches": kl.value,
+                "peak_tf32_burst": tf32["burst"] if tf32 else None, "peak_bf16_sustained_half": tf_sust / 2.0,
+                "hbm_GBps": bytes_ / (k_ms / 1e3) / 1e9, "hbm_frac": bytes_ / (k_ms / 1e3) / 1e9 / hbm_peak,
+                "hbm_frac_nominal_8tbs": bytes_ / (k_ms / 1e3) / 1e9 / HBM_NOMINAL_GBS,
+                "note": "achieved = algorithmic 2*N*D*B flops per launch of the dominant kernel / its CUDA-event "
+                        "duration; peak = %s; hbm_* = N*ld*4 database bytes / the same duration against the %s copy "
+                        "peak %.0f GB/s" % (peak_note, which, hbm_peak)}
+        if screen:
+            roof["screening"] = screen
     else:
-        # the same kernel timed as 200 back-to-back launches inside the library (no Python between launches)
-        b2b = ctypes.c_float()
-        lib.cslam_nns_time_search(h.h, ctypes.c_void_p(qb[0].data_ptr()), batch, dim, k, 200,
-                                  ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), ctypes.byref(b2b))
         bytes_ = float(local_rows) * ((dim + 3) // 4 * 4) * 4
         achieved = bytes_ / (k_ms / 1e3) / 1e9
+        b2b_ms = b2b.value / max(1, batch)
         roof = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "kernel": "k1_single_query",
-                "kernel_ms": k_ms, "launches": kl.value, "kernel_ms_back_to_back": b2b.value / max(1, batch),
-                "note": "achieved = N*ld*4 algorithmic bytes per launch / CUDA-event duration; peak = %s "
-                        "copy bandwidth" % which}
+                "frac": achieved / hbm_peak, "frac_nominal_8tbs": achieved / HBM_NOMINAL_GBS,
+                "traffic": None, "kernel": "k1_single_query",
+                "kernel_ms": k_ms, "launches": kl.value, "kernel_ms_back_to_back": b2b_ms,
+                "back_to_back_GBps": bytes_ / (b2b_ms / 1e3) / 1e9,
+                "back_to_back_frac": bytes_ / (b2b_ms / 1e3) / 1e9 / hbm_peak,
+                "back_to_back_frac_nominal_8tbs": bytes_ / (b2b_ms / 1e3) / 1e9 / HBM_NOMINAL_GBS,
+                "note": "achieved = N*ld*4 algorithmic bytes per launch / CUDA-event duration of each launch in the "
+                        "bench's Python-driven stream; back_to_back = the same search queued 200x inside the "
+                        "library; peak = %s copy bandwidth" % which}
 
     # traffic: DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of this
     # workload (profiles/ncu_traffic.json), null when none exists for it
     try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.workload)
-        if tr and world == 1 and not (args.rows or args.dim or args.batch or args.k):
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(name)
+        if tr and world == 1 and not overridden:
             roof["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
             roof["traffic_source"] = tr["source"]
             if "tensor_pipe_active_pct" in tr:   # sm__pipe_tensor_cycles_active, same capture
@@ -584,25 +805,78 @@ def main():
 
     cpu = None
     if not args.no_cpu_baseline:
-        v, cores, desc = cpu_port_qps(rows, dim, batch, k)
-        cpu = {"value": v, "unit": "queries/s", "cores": cores, "kind": "port", "sample": desc}
+        cpu = cpu_baseline_block(rows, dim, batch, k, cpu_budget)
 
-    line = {"metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products, fp32 accumulate)"
-            if variant == 2 else "f32", "data": "synthetic",
-            "config": dict(workload_config(args, rows, dim, batch, k), search_variant=variant,
+    line = {"metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": world, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32 (tf32 tensor-core products, fp32 accumulate; every returned similarity is an fp32-exact "
+                     "3xTF32 or fp32 re-scored value)" if variant == 2 else "f32", "data": "synthetic",
+            "config": dict(workload_config(name, world, rows, dim, batch, k), search_variant=variant,
                            **({"step": "1 add_item (one new row) + 1 search; the database grows by one row per step"}
                               if incremental else {}),
                            **({"exchange": "K5 peer-memory kernel (csrc/k5_exchange.cu)"
-                               if getattr(m, "_xchg", None) is not None else "NCCL all-gather + K4"} if world > 1 else {})),
-            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches)}
-    if torch_bar is not None:
-        line["torch_cuda_reference"] = torch_bar
-    print(json.dumps(line))
-    if world > 1:
+                               if xchg_peer else "NCCL all-gather + K4"} if world > 1 else {})),
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks, "gpu_launches": int(launches),
+            "parity": parity}
+    if gpu_ref is not None:
+        line["gpu_reference"] = gpu_ref
+    return line, ok
+
+
+def leg_steps(name, steps):
+    """Short legs: enough steps for a stable figure, bounded so that the default run stays within minutes."""
+    return {"c2": max(steps, 1000), "c2_k10": max(steps, 1000), "c4": max(steps, 300), "c5": max(steps, 10),
+            "swarm": max(steps, 200)}.get(name, steps)
+
+
+def main():
+    args = parse()
+    if args.workload == "sc":
+        return bench_scancontext(args)
+    name = args.workload or "c3"
+    if name == "swarm":
+        if args.impl == "reference":   # the CPU arm of one per-robot database: BASELINE configs[3]'s shape
+            return reference_arm(args, "c4", (args.rows or 2_000_000) // args.robots, args.dim or 256, 1, 1)
+        line = run_swarm(args, args.steps, args.warmup)
+        print(json.dumps(line))
+        return 0 if (line["parity"] is None or line["parity"]["ok"]) else 3
+    rows, dim, batch, k, _ = WORKLOADS[name]
+    overridden = bool(args.rows or args.dim or args.batch or args.k)
+    rows, dim, batch, k = args.rows or rows, args.dim or dim, args.batch or batch, args.k or k
+    if args.impl == "reference":
+        return reference_arm(args, name, rows, dim, batch, k)
+
+    import torch.distributed as dist
+    ctx = Ctx(args)
+    line, ok = run_dense(ctx, name, rows, dim, batch, k, args.steps, args.warmup, overridden=overridden)
+    all_ok = ok
+    if args.workload is None and not args.no_legs and not overridden:
+        legs = {}
+        names = ["c2", "c2_k10", "c4", "swarm", "c5"] if ctx.world == 1 else ["c5"]
+        for leg in names:
+            if leg == "swarm":
+                l_ = run_swarm(args, leg_steps(leg, args.steps), max(args.warmup, 20), cpu_budget=3.0)
+                ok_ = l_["parity"] is None or l_["parity"]["ok"]
+            else:
+                r_, d_, b_, k_, _ = WORKLOADS[leg]
+                l_, ok_ = run_dense(ctx, leg, r_, d_, b_, k_, leg_steps(leg, args.steps), max(args.warmup, 3),
+                                    cpu_budget=3.0)
+            all_ok = all_ok and ok_
+            if ctx.rank == 0:
+                l_.pop("metric", None)
+                legs[leg] = l_
+        if ctx.rank == 0:
+            line["legs"] = legs
+    if ctx.rank == 0:
+        line["parity_all_ok"] = bool(all_ok)
+        print(json.dumps(line))
+        if not all_ok:
+            sys.stderr.write("PARITY GATE FAILED: see the `parity` blocks of the line above\n")
+    if ctx.world > 1:
         dist.destroy_process_group()
+    return 0 if all_ok else 3
 
 
 if __name__ == "__main__":
-    main()
+    sys.exit(main() or 0)

@@ -96,6 +96,7 @@ struct cslam_nns_s {
   std::vector<long long> ids_host;
   long long ids_synced = 0;  // rows [0, ids_synced) of ids_host are in ids_arena
   // optional per-kernel timing (cslam_nns_profile)
+  cudaEvent_t add_ev = nullptr;  // completion of an append whose host source is pinned (cslam_nns_add)
   bool profile = false;
   std::vector<cudaEvent_t> ev;   // pairs
   size_t ev_used = 0;
@@ -410,6 +411,9 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   if (dim > 0) {
     int rc = cslam_nns_set_dim(h, dim);
     if (rc == 0) rc = grow_to(h, h->initial, 0);
+    // the zero-fill of the new chunk was queued on the legacy stream: finish it here, so that an add or a
+    // search on any (possibly non-blocking) stream can never be overtaken by it
+    if (rc == 0 && cudaStreamSynchronize(0) != cudaSuccess) rc = fail_cuda(h, "cudaStreamSynchronize", cudaGetLastError());
     if (rc != 0) {
       g_create_error = h->err;
       delete h;
@@ -432,6 +436,7 @@ int cslam_nns_destroy(cslam_nns_t h) {
     for (DevBuf* b : bufs) b->free();
     h->res_host.free();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
+    if (h->add_ev) cudaEventDestroy(h->add_ev);
   }
   delete h;
   return 0;
@@ -449,7 +454,9 @@ int cslam_nns_set_dim(cslam_nns_t h, int64_t dim) {
 int cslam_nns_reserve(cslam_nns_t h, int64_t rows) {
   if (!h) return CSLAM_NNS_EINVAL;
   DeviceGuard g(h->device);
-  return grow_to(h, rows, 0);
+  int rc = grow_to(h, rows, 0);
+  if (rc == 0) CK(h, cudaStreamSynchronize(0));  // see cslam_nns_create: the zero-fill must not trail behind
+  return rc;
 }
 
 int64_t cslam_nns_size(cslam_nns_t h) { return h ? h->n : -1; }
@@ -478,6 +485,20 @@ int cslam_nns_add(cslam_nns_t h, const float* rows, int64_t count, int64_t src_l
                             (size_t)count,
                             src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, stream));
     h->n += count;
+    if (!src_is_device) {
+      // Contract (include/cslam_nns.h): a HOST source may be reused as soon as the call returns, like the
+      // reference's synchronous `.to(device)` (nns_matching.py:41).  The driver stages a pageable source
+      // before the copy call returns, but a PINNED (page-locked / registered) source is read by the copy
+      // engine later, asynchronously: wait for that copy — and only for it — before returning.
+      cudaPointerAttributes at;
+      const cudaError_t pe = cudaPointerGetAttributes(&at, rows);
+      if (pe != cudaSuccess) cudaGetLastError();
+      if (pe != cudaSuccess || at.type != cudaMemoryTypeUnregistered) {
+        if (!h->add_ev) CK(h, cudaEventCreateWithFlags(&h->add_ev, cudaEventDisableTiming));
+        CK(h, cudaEventRecord(h->add_ev, stream));
+        CK(h, cudaEventSynchronize(h->add_ev));
+      }
+    }
   }
   if (new_n) *new_n = h->n;
   return 0;

@@ -101,13 +101,15 @@ bool Arena::ensure_vmm(int device, size_t bytes, cudaStream_t stream, std::strin
       return false;
     }
     if (base_) {
-      cudaDeviceSynchronize();  // nothing may be running against the old range
+      // Transactional: the chunks are mapped into the NEW range first (a physical allocation may be mapped
+      // at two addresses), and only when all of them are in place is the old range torn down.  A failure
+      // rolls the new range back and leaves the arena exactly as it was.
       size_t off = 0;
+      bool ok = true;
       for (auto& c : chunks_) {
-        d.memUnmap((CUdeviceptr)base_ + off, c.size);
         if (d.memMap(nb + off, c.size, 0, c.handle, 0) != CUDA_SUCCESS) {
-          *err = "cuMemMap (re-map) failed";
-          return false;
+          ok = false;
+          break;
         }
         off += c.size;
       }
@@ -116,9 +118,23 @@ bool Arena::ensure_vmm(int device, size_t bytes, cudaStream_t stream, std::strin
       acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
       acc.location.id = device;
       acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
-      if (off && d.memSetAccess(nb, off, &acc, 1) != CUDA_SUCCESS) {
-        *err = "cuMemSetAccess (re-map) failed";
+      if (ok && off && d.memSetAccess(nb, off, &acc, 1) != CUDA_SUCCESS) ok = false;
+      if (!ok) {
+        size_t undo = 0;
+        for (auto& c : chunks_) {
+          if (undo >= off) break;
+          d.memUnmap(nb + undo, c.size);
+          undo += c.size;
+        }
+        d.memAddressFree(nb, new_res);
+        *err = "cuMemMap / cuMemSetAccess (re-map into a larger range) failed";
         return false;
+      }
+      cudaDeviceSynchronize();  // nothing may be running against the old range when it goes away
+      size_t old_off = 0;
+      for (auto& c : chunks_) {
+        d.memUnmap((CUdeviceptr)base_ + old_off, c.size);
+        old_off += c.size;
       }
       d.memAddressFree((CUdeviceptr)base_, reserved_);
     }

@@ -83,7 +83,17 @@ __global__ void __launch_bounds__(32) k5_kernel(const XchgDev x, const u64* __re
       __nanosleep(64);
     }
   }
-  if (!__all_sync(kFull, ok) && lane == 0) *x.err = epoch;
+  if (!__all_sync(kFull, ok)) {
+    // a peer never published this query: report the call (mapped host word, read by cslam_nns_xchg_status
+    // right after the caller's synchronisation) and return "no result" for the query instead of a merge of
+    // whatever the buffers hold
+    if (lane == 0) *x.err = epoch;
+    if (lane < k) {
+      if (out_idx) out_idx[(size_t)b * k + lane] = -1ll;
+      if (out_sim) out_sim[(size_t)b * k + lane] = -INFINITY;
+    }
+    return;
+  }
   u64 thr = 0ull, mine = 0ull;
   const u64* mykeys = x.keys[x.rank] + (size_t)parity * x.world * kXchgCap + (size_t)b * k;
   for (int r = 0; r < x.world; ++r) {

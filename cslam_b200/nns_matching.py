@@ -126,6 +126,27 @@ class NearestNeighborsMatching(object):
             self._view_key = key
         return self._view
 
+    @data.setter
+    def data(self, value):
+        """The reference's ``data`` is a plain attribute; assigning a ``(rows, dim)`` tensor/array here copies it
+        into the HBM arena (capacity grows to hold it, ``n`` is left alone exactly as a rebinding would)."""
+        if self._h is None and isinstance(value, (list, tuple)) and len(value) == 0:
+            return
+        value = torch.as_tensor(value)
+        if value.dim() != 2:
+            raise ValueError("data must be a (rows, dim) matrix")
+        if self.dim is None:
+            self.dim = int(value.shape[1])
+        if int(value.shape[1]) != self.dim:
+            raise RuntimeError("data has %d columns, the matcher's dim is %d" % (value.shape[1], self.dim))
+        h = self._open()
+        _native.check(h.lib.cslam_nns_reserve(h.h, int(value.shape[0])), h.h)
+        view = self.data
+        view[:value.shape[0]].copy_(value.to(torch.float32))
+        if view.shape[0] > value.shape[0]:
+            view[value.shape[0]:].zero_()
+        torch.cuda.current_stream(view.device).synchronize()
+
     # -- add_item (reference: nns_matching.py:23-42) ------------------------------------------------
     def add_item(self, vector, item):
         """Add item to the matching list.
@@ -186,6 +207,8 @@ class NearestNeighborsMatching(object):
         if not msgs:
             return
         dim = len(msgs[0].descriptor) if self.dim is None else self.dim
+        # pinned staging: cslam_nns_add waits for the copy of a pinned source before it returns (see the
+        # contract in include/cslam_nns.h), so the block can go back to torch's pinned cache right after
         staging = torch.empty((len(msgs), dim), dtype=torch.float32,
                               pin_memory=torch.cuda.is_available())
         block = staging.numpy()
@@ -193,21 +216,36 @@ class NearestNeighborsMatching(object):
             block[j] = np.asarray(m.descriptor, dtype=np.float32)   # raises on a wrong length
         self.add_items(staging, [m.keyframe_id for m in msgs])
 
-    def save(self, path):
+    def save(self, path, allow_pickle=False):
         """Write the database (rows 0..n-1 exactly as stored, and the row -> item map) to ``path`` (.npz).
-        The reference has no persistence; this is what a restart needs."""
-        import pickle
+        The reference has no persistence; this is what a restart needs.  Integer items (keyframe
+        ids, the production case) are stored as a plain int64 array; arbitrary Python items need
+        ``allow_pickle=True`` on both ``save`` and ``load`` (a pickled payload runs code when loaded)."""
         rows = self.data[:self.n].cpu().numpy() if self.n else np.zeros((0, self.dim or 0), np.float32)
+        items = [self.items[i] for i in range(self.n)]
+        if all(type(it) is int and -2 ** 63 <= it < 2 ** 63 for it in items):
+            np.savez(path, data=rows, dim=np.int64(self.dim or 0), item_ids=np.asarray(items, dtype=np.int64))
+            return
+        if not allow_pickle:
+            raise TypeError("items are not all Python ints: pass allow_pickle=True to store them pickled "
+                            "(only load such a file from a source you trust)")
+        import pickle
         np.savez(path, data=rows, dim=np.int64(self.dim or 0),
-                 items=np.frombuffer(pickle.dumps([self.items[i] for i in range(self.n)]), dtype=np.uint8))
+                 items=np.frombuffer(pickle.dumps(items), dtype=np.uint8))
 
     @classmethod
-    def load(cls, path):
-        """Rebuild a matcher from ``save``'s file: one bulk append, identical rows and items."""
-        import pickle
-        z = np.load(path if str(path).endswith(".npz") else str(path) + ".npz")
+    def load(cls, path, allow_pickle=False):
+        """Rebuild a matcher from ``save``'s file: one bulk append, identical rows and items.  A file whose
+        items were pickled is refused unless ``allow_pickle=True``."""
+        z = np.load(path if str(path).endswith(".npz") else str(path) + ".npz", allow_pickle=False)
         m = cls()
-        items = pickle.loads(z["items"].tobytes())
+        if "item_ids" in z.files:
+            items = z["item_ids"].tolist()
+        elif not allow_pickle:
+            raise ValueError("%s stores pickled items: pass allow_pickle=True if the file is trusted" % (path,))
+        else:
+            import pickle
+            items = pickle.loads(z["items"].tobytes())
         if len(items):
             m.add_items(z["data"], items)
         elif int(z["dim"]) > 0:

@@ -57,6 +57,17 @@ def merge_keys_host(keys, k):
     return rows, sims
 
 
+class RowIdentity(object):
+    """``items`` of a bulk-loaded shard set (``add_local_shard``): the item of global row ``i`` is ``i``.
+    A mapping without storage, so that a 10M-row benchmark database does not need a 10M-entry dict."""
+
+    def __getitem__(self, i):
+        return i
+
+    def __len__(self):
+        return 0
+
+
 class ShardedNearestNeighborsMatching(object):
     """Same three methods as the reference matcher; every rank calls them with the same arguments."""
 
@@ -73,6 +84,7 @@ class ShardedNearestNeighborsMatching(object):
         self.dim = dim
         self._xchg = None     # peer-memory exchange (K5), opened lazily on the first device search
         self._xchg_tried = False
+        self._q_stage = None  # device staging of the query block for search_batch (slice upload + all-gather)
 
     # -- peer-memory exchange ----------------------------------------------------------------------
     def _exchange(self, device):
@@ -150,6 +162,17 @@ class ShardedNearestNeighborsMatching(object):
         if self.world > 1:
             dist.all_reduce(t, group=self.group)
         self.n = int(t.item())
+        if not self.items:
+            self.items = RowIdentity()
+
+    def _check_exchange(self):
+        """After a host synchronisation: a K5 wait that timed out (dead or out-of-step peer) left -1 / -inf
+        in the affected queries; report it for THIS call instead of on the next one."""
+        if self._xchg is not None:
+            lib = _native.load()
+            if lib.cslam_nns_xchg_status(self._xchg) != _native.OK:
+                why = lib.cslam_nns_xchg_last_error(self._xchg).decode("utf-8", "replace")
+                raise _native.NativeError(_native.ECUDA, "peer-memory exchange failed: %s" % why)
 
     # -- search ------------------------------------------------------------------------------------
     def search_keys_device(self, q_dev, k):
@@ -167,8 +190,10 @@ class ShardedNearestNeighborsMatching(object):
         _native.check(rc, h.h)
         return keys
 
-    def search_batch_device(self, q_dev, k, out_idx=None, out_sim=None):
-        """Device in, device out: (global rows int64 [B,k], sims f32 [B,k]); -1/-inf past the end."""
+    def search_batch_device(self, q_dev, k, out_idx=None, out_sim=None, exchange=None):
+        """Device in, device out: (global rows int64 [B,k], sims f32 [B,k]); -1/-inf past the end.
+        Stream-ordered, no host synchronisation; callers that synchronise themselves should call
+        ``check_exchange()`` afterwards.  ``exchange="nccl"`` forces the all-gather + K4 route for this call."""
         q_dev = q_dev.contiguous()
         B = int(q_dev.shape[0])
         if self.world == 1 and self.local._h is not None and self.local.n >= k:
@@ -185,7 +210,8 @@ class ShardedNearestNeighborsMatching(object):
         if out_idx is None:
             out_idx = torch.empty((B, k), dtype=torch.int64, device=q_dev.device)
             out_sim = torch.empty((B, k), dtype=torch.float32, device=q_dev.device)
-        xchg = self._exchange(q_dev.device) if (k <= 32 and B <= 4096 and B * k <= 131072) else None
+        xchg = self._exchange(q_dev.device) if (k <= 32 and B <= 4096 and B * k <= 131072
+                                                and exchange != "nccl") else None
         if xchg is not None:
             # local search + exchange + merge in ONE C-ABI call (cslam_nns_search_sharded)
             if self.local.dim is None and self.dim is not None:
@@ -210,7 +236,32 @@ class ShardedNearestNeighborsMatching(object):
         _native.check(rc, None)
         return out_idx, out_sim
 
-    def search_batch(self, queries, k):
+    def check_exchange(self):
+        """Raise if a peer-memory exchange of an earlier ``search_batch_device`` call timed out (call after
+        synchronising the stream)."""
+        self._check_exchange()
+
+    def _upload_queries(self, q_host):
+        """Host query block (identical on every rank) -> device.  With several ranks each one uploads only ITS
+        1/world slice over its own PCIe link and one all-gather over NVLink completes the block on every GPU
+        (world identical 4 MB uploads cost more than the kernel they feed at 8 GPUs)."""
+        B, dim = int(q_host.shape[0]), int(q_host.shape[1])
+        dev = torch.device("cuda", torch.cuda.current_device())
+        if self.world == 1 or not dist.is_initialized() or B < 4 * self.world:
+            return q_host.to(dev, non_blocking=True)
+        per = (B + self.world - 1) // self.world
+        if self._q_stage is None or self._q_stage.shape[0] != self.world * per or self._q_stage.shape[1] != dim:
+            self._q_stage = torch.empty((self.world * per, dim), dtype=torch.float32, device=dev)
+        lo, hi = min(self.rank * per, B), min((self.rank + 1) * per, B)
+        mine = self._q_stage[self.rank * per:(self.rank + 1) * per]
+        if hi > lo:
+            mine[:hi - lo].copy_(q_host[lo:hi], non_blocking=True)
+        dist.all_gather_into_tensor(self._q_stage, mine, group=self.group)
+        return self._q_stage[:B]
+
+    def search_batch(self, queries, k, root_only=False):
+        """Host queries in, host results out.  ``root_only=True``: only rank 0 reads the results back
+        (every rank holds identical results on the device; the others return ``(None, None)``)."""
         if not torch.is_tensor(queries):
             queries = torch.from_numpy(np.asarray(queries).astype(np.float32))
         k = int(k)
@@ -218,9 +269,15 @@ class ShardedNearestNeighborsMatching(object):
         B = int(queries.reshape(-1, self.dim).shape[0]) if self.dim else 0
         if kk == 0 or B == 0:
             return [[] for _ in range(B)], np.empty((B, 0), np.float32)
-        q = queries.reshape(-1, self.dim).to(torch.float32).cuda(non_blocking=True)
+        q = queries.reshape(-1, self.dim).to(torch.float32)
+        q = q if q.is_cuda else self._upload_queries(q)
         idx, sims = self.search_batch_device(q, kk)
+        if root_only and self.rank != 0:
+            torch.cuda.current_stream().synchronize()
+            self._check_exchange()
+            return None, None
         idx, sims = idx.cpu().numpy(), sims.cpu().numpy()
+        self._check_exchange()
         return [[self.items[i] for i in row] for row in idx.tolist()], sims
 
     def search(self, query, k):

@@ -72,13 +72,20 @@ int64_t cslam_nns_size(cslam_nns_t h);      /* n */
 int64_t cslam_nns_capacity(cslam_nns_t h);  /* len(self.data) */
 int64_t cslam_nns_dim(cslam_nns_t h);       /* 0 while undecided */
 int64_t cslam_nns_ld(cslam_nns_t h);        /* row pitch in floats (dim rounded up to 4) */
-void* cslam_nns_data_ptr(cslam_nns_t h);    /* device pointer of row 0; stable for the handle's life */
+void* cslam_nns_data_ptr(cslam_nns_t h);    /* device pointer of row 0; changes only when the reserved virtual
+                                               range itself is outgrown (re-map, no copy): re-read after adds */
 int cslam_nns_device(cslam_nns_t h);
 
 /* -- add_item (nns_matching.py:23-42) ----------------------------------------------------------- */
 
 /* Append `count` rows of `dim` fp32 values (row pitch src_ld floats, >= dim; 0 means dim).
- * Stream-ordered; the source buffer may be reused as soon as the call returns.
+ * Stream-ordered with respect to later calls on the same stream.  Source lifetime:
+ *   - HOST source, pageable or pinned: may be reused / freed as soon as the call returns (the semantics of the
+ *     reference's synchronous `vector.to(device)`, nns_matching.py:41).  For a pinned (page-locked or
+ *     cudaHostRegister'ed) source the copy engine reads the buffer asynchronously, so the call waits for THAT
+ *     copy (an event, not the whole stream) before returning;
+ *   - DEVICE source: stream-ordered — it may be overwritten by work queued on the same stream after the call;
+ *     work on other streams (or the host) must first synchronise with `stream`.
  * *new_n (optional) receives the row count after the append. */
 int cslam_nns_add(cslam_nns_t h, const float* rows, int64_t count, int64_t src_ld,
                   int src_is_device, void* stream, int64_t* new_n);
