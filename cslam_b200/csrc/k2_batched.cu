@@ -442,12 +442,30 @@ __global__ void k2_prepare_kernel(const float* __restrict__ q, int dim, int q_ld
       t += red[0][w];
       u += red[1][w];
     }
-    inv_qn[b] = 1.0f / fmaxf(sqrtf(t), kEps);
+    const float invq = 1.0f / fmaxf(sqrtf(t), kEps);
+    inv_qn[b] = invq;
     const float c = u / (float)dim;
     mean_s = (c == c && fabsf(c) < 3.0e38f) ? c : 0.f;  // NaN/Inf queries: no centring
     q_mean[b] = mean_s;
-    // third plane: the grid-wide per-query lower bound of the k-th best similarity (ordered-uint), 0 = none yet
-    reinterpret_cast<unsigned*>(q_mean + gridDim.x)[b] = 0u;
+    const int B = (int)gridDim.x;
+    // planes 2 and 3: the grid-wide per-query lower bounds of the k-th best similarity (ordered uint, 0 = none
+    // yet) of the first pass (the only one, or the screening pass) and of the masked fallback pass
+    reinterpret_cast<unsigned*>(inv_qn + kQParGthr * B)[b] = 0u;
+    reinterpret_cast<unsigned*>(inv_qn + kQParGthrFull * B)[b] = 0u;
+    // plane 4: E_q, a bound on |screened similarity - exact fp32 similarity| for ANY row (k6_rescore.cu has
+    // the derivation): operands cut to tf32 (2^-10 relative each: 2^-9 of sum |x_i||q_i - c| <= |x||q - c|),
+    // fp32 accumulation in tensor memory (dim / 8 instructions, bounded generously by dim ulps), the fp32 sums
+    // |x|^2 and sum(x) of the converter (dim / 4 sequential adds), epilogue and re-scoring roundings; x 1.25
+    const float dev2 = fmaxf(t - (float)dim * mean_s * mean_s, 0.f);      // |q - c|^2
+    const float rho = sqrtf(dev2) * invq;
+    const float fd = (float)dim;
+    const float e = (1.953125e-3f + fd * 1.1920929e-7f) * rho +
+                    (0.25f * fd + 8.f) * 5.9604645e-8f * (1.f + fabsf(mean_s) * sqrtf(fd) * invq) + 2e-6f;
+    inv_qn[kQParEbound * B + b] = 1.25f * e;      // NaN for a NaN query: every comparison fails -> fallback
+    if (b == 0) {
+      unsigned* w = reinterpret_cast<unsigned*>(inv_qn + kQParPlanes * B);
+      for (int i = 0; i < kQParTailWords; ++i) w[i] = 0u;   // fail mask [0..7], fail count [8]
+    }
   }
   __syncthreads();
   const float c = mean_s;
@@ -528,7 +546,7 @@ int k2s_grid(long long n, int num_sms) {
 // q_lo buffer layout: [q_hi plane (B x q_ld)][q_lo plane (B x q_ld)] — callers size it 2x
 cudaError_t k2_prepare(const float* q, int B, int dim, int q_ld, float* q_planes, float* inv_qn,
                        cudaStream_t stream) {
-  // inv_qn buffer layout: [inv_qn (B)][q_mean (B)][shared threshold (B, u32)] — callers size it 3x
+  // inv_qn buffer layout: kQParPlanes planes of B words + kQParTailWords words (kernels.h) — callers size it so
   const int threads = dim >= 2048 ? 512 : (dim >= 512 ? 256 : 128);  // three latency-bound passes per block
   k2_prepare_kernel<<<B, threads, 0, stream>>>(q, dim, q_ld, q_planes, q_planes + (size_t)B * q_ld, inv_qn,
                                           inv_qn + B);

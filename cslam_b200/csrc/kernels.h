@@ -53,7 +53,28 @@ cudaError_t sort_select(const float* all_sims, long long n, int k, void* temp, s
 // keys laid out [parts][B][k_in]; writes B x k_out (k_out <= k_in is fine).
 cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_out, u64* out_keys,
                      long long* out_idx, float* out_sim, long long idx_stride,
-                     long long idx_offset, cudaStream_t stream, const unsigned* floor_ord = nullptr);
+                     long long idx_offset, cudaStream_t stream, const unsigned* floor_ord = nullptr,
+                     const unsigned* active_mask = nullptr);
+// whether the batched search of B queries may take the screening route (query-major tiling, k2_qm.cu)
+bool k2_screen_supported(int B, int k, int dim);
+
+// ---- K6: exact fp32 re-scoring of the screening pass's candidates, with the completeness proof (k6_rescore.cu)
+struct K6Args {
+  const float* db;
+  long long n;
+  int ld, dim;
+  const float* q;        // raw fp32 queries [B][q_ld]
+  int q_ld;
+  const float* qpar;     // the k2_prepare parameter block
+  const u64* part_keys;  // [parts][B][k] lists of the screening pass
+  int parts, B, k;
+  u64* out_keys;
+  long long* out_idx;
+  float* out_sim;
+  long long idx_stride, idx_offset;
+  unsigned long long* stats;  // [0] += queries screened, [1] += queries handed to the fallback
+};
+cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream);
 // the per-query shared threshold plane the query-major batched kernel leaves behind ([B] ordered uints inside
 // the inv_qn buffer), or null when the batch was served by the row-major kernel
 const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim);
@@ -64,6 +85,16 @@ static constexpr int kK2MaxBatch = 256;  // queries per pass (UMMA N)
 // share the 512 columns of tensor memory
 static constexpr int kRowsMaxBatch = 192;
 static constexpr int kK2ListBudget = 2560;  // k * padded batch must not exceed this (smem lists)
+
+// Per-batch query parameter block written by k2_prepare: kQParPlanes planes of B 32-bit words, then a tail.
+static constexpr int kQParInv = 0;       // 1 / max(|q|, eps)
+static constexpr int kQParMean = 1;      // mean(q) (the centring constant)
+static constexpr int kQParGthr = 2;      // shared k-th-best lower bound of the first pass (ordered uint)
+static constexpr int kQParGthrFull = 3;  // the same for the masked 3xTF32 fallback pass
+static constexpr int kQParEbound = 4;    // E_q: bound on |screened - exact| similarity
+static constexpr int kQParPlanes = 5;
+static constexpr int kQParTailWords = 16;  // [0..7] mask of queries the screening could not prove, [8] their count
+static inline size_t k2_qpar_bytes(int B) { return ((size_t)kQParPlanes * B + kQParTailWords) * 4; }
 
 struct K2Args {
   const float* db;
@@ -77,6 +108,13 @@ struct K2Args {
   int k;
   u64* part_keys;      // [grid][B][k] scratch
   void* encode_fn;     // cuTensorMapEncodeTiled entry point
+  // query-major kernel only.  screen: ONE tf32 product (q_hi plane, raw rows), read-only converter — the
+  // similarities are approximate and the lists feed k6_rescore.  active_mask / active_count (device): the
+  // masked fallback — only the queries whose bit is set are searched, and the whole grid exits at once when
+  // *active_count == 0 (the launch is queued unconditionally, without a host round trip).
+  bool screen = false;
+  const unsigned* active_mask = nullptr;
+  const unsigned* active_count = nullptr;
 };
 bool k2_supported(int B, int k, int dim);
 // number of partial key lists [parts][B][k] a launch for batch B writes (sizes part_keys, feeds k4_merge)
