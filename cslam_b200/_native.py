@@ -53,6 +53,8 @@ SIGNATURES = {
     "cslam_nns_profile_read": (_c.c_int, [_handle, _c.POINTER(_c.c_float), _c.POINTER(_i64)]),
     "cslam_nns_set_variant": (_c.c_int, [_handle, _c.c_int]),
     "cslam_nns_last_variant": (_c.c_int, [_handle]),
+    "cslam_nns_set_screen": (_c.c_int, [_handle, _c.c_int, _i64]),
+    "cslam_nns_screen_stats": (_c.c_int, [_handle, _c.POINTER(_i64), _c.POINTER(_i64)]),
     "cslam_nns_time_search": (_c.c_int, [_handle, _f32p, _i64, _i64, _c.c_int, _c.c_int,
                                          _c.c_void_p, _c.POINTER(_c.c_float)]),
 }

@@ -90,6 +90,9 @@ struct cslam_nns_s {
   K1Tuning k1;
   // device scratch
   DevBuf q, q_lo, inv_qn, scratch, ticket, part_keys, res_dev, all_sims, sort_tmp, sort_kv, qids, shard_keys;
+  DevBuf screen_stats;             // [2] u64: queries screened / handed to the 3xTF32 fallback
+  bool screen = true;              // screening route enabled (CSLAM_NNS_SCREEN=0 or cslam_nns_set_screen disable it)
+  long long screen_min_rows = 8192;  // below this the second and third launch cost more than the 3xTF32 pass saves
   PinBuf res_host;
   // integer row identities for the device-side candidate filter (cslam_nns_search_filtered)
   Arena ids_arena;
@@ -312,7 +315,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
   for (long long b0 = 0; b0 < B; b0 += kK2MaxBatch) {
     const int Bc = (int)((B - b0) > kK2MaxBatch ? kK2MaxBatch : (B - b0));
     const int grid = k2_parts(h->n, Bc, h->dim, h->num_sms);
-    if (!h->q_lo.ensure((size_t)2 * Bc * q_ld * 4) || !h->inv_qn.ensure((size_t)3 * Bc * 4) ||
+    if (!h->q_lo.ensure((size_t)2 * Bc * q_ld * 4) || !h->inv_qn.ensure(k2_qpar_bytes(Bc)) ||
         !h->part_keys.ensure((size_t)grid * Bc * k_run * 8))
       return fail(h, CSLAM_NNS_ENOMEM, "batched scratch");
     const float* qc = dq + b0 * q_ld;
@@ -330,16 +333,62 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
     a.k = k_run;
     a.part_keys = (u64*)h->part_keys.p;
     a.encode_fn = d.tensorMapEncodeTiled;
+    u64* ok_ = o_keys ? o_keys + b0 * k_run : nullptr;
+    long long* oi_ = o_idx ? o_idx + b0 * k_run : nullptr;
+    float* os_ = o_sim ? o_sim + b0 * k_run : nullptr;
     const char* kerr = nullptr;
     cudaError_t e;
+    // Screening route (large batches, big enough databases): ONE tf32 product over the whole database, exact
+    // fp32 re-scoring of the few candidates per query with a completeness proof (k6_rescore.cu), and the 3xTF32
+    // pass only for the queries the proof does not cover — queued unconditionally, it exits at once when there
+    // are none, so the call stays stream-ordered without a host round trip.
+    const bool screen = h->screen && h->n >= h->screen_min_rows && k2_screen_supported(Bc, k_run, (int)h->dim);
+    if (screen) {
+      if (!h->screen_stats.p) {
+        if (!h->screen_stats.ensure(16)) return fail(h, CSLAM_NNS_ENOMEM, "screening counters");
+        CK(h, cudaMemsetAsync(h->screen_stats.p, 0, 16, stream));
+      }
+      a.screen = true;
+      {
+        KernelTimer kt(h, stream);
+        e = k2_launch(a, h->num_sms, stream, &kerr);
+      }
+      if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (screening)", e);
+      K6Args r;
+      r.db = a.db;
+      r.n = a.n;
+      r.ld = a.ld;
+      r.dim = a.dim;
+      r.q = qc;
+      r.q_ld = (int)q_ld;
+      r.qpar = a.inv_qn;
+      r.part_keys = a.part_keys;
+      r.parts = grid;
+      r.B = Bc;
+      r.k = k_run;
+      r.out_keys = ok_;
+      r.out_idx = oi_;
+      r.out_sim = os_;
+      r.idx_stride = idx_stride;
+      r.idx_offset = idx_offset;
+      r.stats = (unsigned long long*)h->screen_stats.p;
+      CK(h, k6_rescore(r, stream));
+      const unsigned* tail = (const unsigned*)h->inv_qn.p + (size_t)kQParPlanes * Bc;
+      a.screen = false;
+      a.active_mask = tail;
+      a.active_count = tail + 8;
+      e = k2_launch(a, h->num_sms, stream, &kerr);
+      if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (fallback)", e);
+      CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run, ok_, oi_, os_, idx_stride, idx_offset,
+                     stream, (const unsigned*)h->inv_qn.p + (size_t)kQParGthrFull * Bc, tail));
+      continue;
+    }
     {
       KernelTimer kt(h, stream);
       e = k2_launch(a, h->num_sms, stream, &kerr);
     }
     if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch", e);
-    CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run,
-                   o_keys ? o_keys + b0 * k_run : nullptr, o_idx ? o_idx + b0 * k_run : nullptr,
-                   o_sim ? o_sim + b0 * k_run : nullptr, idx_stride, idx_offset, stream,
+    CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run, ok_, oi_, os_, idx_stride, idx_offset, stream,
                    k2_floor_plane((const float*)h->inv_qn.p, Bc, h->dim)));
   }
   return 0;
@@ -407,6 +456,8 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->k1.stages = env_int("CSLAM_K1_STAGES", 2);  // 8 KB x 2 per warp: best of the B200 sweep (profiles/r1_k1_sweep_v2.log)
   h->k1.ctas = env_int("CSLAM_K1_CTAS", 0);
   h->variant = env_int("CSLAM_NNS_VARIANT", 0);
+  h->screen = env_int("CSLAM_NNS_SCREEN", 1) != 0;
+  h->screen_min_rows = env_int("CSLAM_NNS_SCREEN_MIN_ROWS", 8192);
   *out = h;
   if (dim > 0) {
     int rc = cslam_nns_set_dim(h, dim);
@@ -431,7 +482,7 @@ int cslam_nns_destroy(cslam_nns_t h) {
     cudaDeviceSynchronize();
     h->arena.release();
     h->ids_arena.release();
-    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket, &h->qids, &h->shard_keys,
+    DevBuf* bufs[] = {&h->q,         &h->q_lo,    &h->inv_qn,   &h->scratch,  &h->ticket, &h->qids, &h->shard_keys, &h->screen_stats,
                       &h->part_keys, &h->res_dev, &h->all_sims, &h->sort_tmp, &h->sort_kv};
     for (DevBuf* b : bufs) b->free();
     h->res_host.free();
@@ -819,6 +870,25 @@ int cslam_nns_set_variant(cslam_nns_t h, int variant) {
   return 0;
 }
 int cslam_nns_last_variant(cslam_nns_t h) { return h ? h->last_variant : -1; }
+
+int cslam_nns_set_screen(cslam_nns_t h, int enable, int64_t min_rows) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  h->screen = enable != 0;
+  if (min_rows >= 0) h->screen_min_rows = min_rows;
+  return 0;
+}
+
+int cslam_nns_screen_stats(cslam_nns_t h, int64_t* screened, int64_t* fallback) {
+  if (!h) return CSLAM_NNS_EINVAL;
+  unsigned long long v[2] = {0ull, 0ull};
+  if (h->screen_stats.p) {
+    DeviceGuard g(h->device);
+    CK(h, cudaMemcpy(v, h->screen_stats.p, sizeof v, cudaMemcpyDeviceToHost));
+  }
+  if (screened) *screened = (int64_t)v[0];
+  if (fallback) *fallback = (int64_t)v[1];
+  return 0;
+}
 
 int cslam_nns_time_search(cslam_nns_t h, const float* queries_dev, int64_t B, int64_t q_ld, int k,
                           int iters, void* stream_, float* ms_per_search) {

@@ -570,10 +570,10 @@ cudaError_t k2s_launch(const K2Args& a, int num_sms, cudaStream_t stream, const 
   if (env_stages >= 2 && env_stages < p.xslots) p.xslots = env_stages;
   p.dbg = env_dbg;
   p.kblocks = (a.dim + BK - 1) / BK;
-  p.inv_qn = a.inv_qn;
-  p.q_mean = a.inv_qn + a.B;
+  p.inv_qn = a.inv_qn + kQParInv * a.B;
+  p.q_mean = a.inv_qn + kQParMean * a.B;
   p.part_keys = a.part_keys;
-  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn + 2 * a.B));  // zeroed by k2_prepare
+  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn)) + kQParGthr * a.B;  // zeroed by k2_prepare
   // kind::tf32, fp32 accumulate, both operands K-major: c_format=F32(1)<<4, a/b_format=TF32(2)<<7/<<10,
   // N>>3 at bit 17, M>>4 at bit 24
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);

@@ -54,6 +54,9 @@ struct QDev {
   unsigned* gthr;  // [B] grid-wide lower bound of each query's k-th best similarity (ordered uint), 0 = none
   u64* part_keys;  // [2 * pairs][B][k]
   u64* prof;
+  // masked fallback pass: only queries whose bit is set take part, and the grid exits when *active_count == 0
+  const unsigned* active_mask;
+  const unsigned* active_count;
 };
 
 struct QSmem {
@@ -61,14 +64,17 @@ struct QSmem {
   uint32_t lists_off, norm_off, bars_off, tmem_off, total;
 };
 
-template <int BK>
+// SCREEN: the screening pass stages the raw database tile (the tensor core cuts it to tf32 itself) and ONE
+// query plane: 2 tiles per stage instead of 4, so the ring is twice as deep and the L2 -> shared-memory
+// traffic per K block drops from 3 units (x, q_hi, q_lo) to 2
+template <int BK, bool SCREEN>
 __host__ __device__ inline QSmem qcarve(int k, int stages) {
   QSmem s;
   s.tile_bytes = BM * BK * 4;
   s.x_lo_off = s.tile_bytes;
-  s.q_hi_off = 2 * s.tile_bytes;
+  s.q_hi_off = (SCREEN ? 1 : 2) * s.tile_bytes;
   s.q_lo_off = 3 * s.tile_bytes;
-  s.stage_bytes = 4 * s.tile_bytes;  // 16 KB (BK = 32) or 8 KB (BK = 16) per tile: multiple of 1024
+  s.stage_bytes = (SCREEN ? 2 : 4) * s.tile_bytes;  // 16 KB (BK = 32) or 8 KB (BK = 16) per tile: multiple of 1024
   uint32_t o = s.stage_bytes * (uint32_t)stages;
   s.lists_off = o;  o += 2u * BM * k * 8;              // [2 column halves][k][128] keys
   s.norm_off = o;   o += 2u * 2u * BN2 * 4;            // [2 accumulators][inv|x| (256), sum(x) (256)]
@@ -195,14 +201,17 @@ __device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq,
   return st;
 }
 
-template <int BK>
+template <int BK, bool SCREEN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
            const QDev p) {
+  // masked fallback pass, queued unconditionally behind the screening pass: nothing to do when every query's
+  // candidate set was proven complete (uniform over the grid, before any barrier or allocation)
+  if (p.active_count != nullptr && __ldcg(p.active_count) == 0u) return;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // identical layout in both CTAs (the pair MMA addresses the peer's operands by the leader's offsets)
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  const QSmem L = qcarve<BK>(p.k, p.stages);
+  const QSmem L = qcarve<BK, SCREEN>(p.k, p.stages);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int S = p.stages;
   const uint32_t rank = cluster_ctarank();
@@ -276,7 +285,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       for (long long t = 0; t < my_tiles; ++t) {
         for (int kb = 0; kb < p.kblocks; ++kb, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
           QPROF_WAIT(w0, mbar_wait(&empty_bar[s], ph ^ 1));
-          if (rank == 0) mbar_expect_tx(&qfull_bar[s], 4u * L.tile_bytes);
+          if (rank == 0) mbar_expect_tx(&qfull_bar[s], (SCREEN ? 2u : 4u) * L.tile_bytes);  // both CTAs' boxes
           tma_load_3d_pair(smem + (size_t)s * L.stage_bytes + L.q_hi_off, &map_q, kb * BK, (int)rank * BM, 0,
                            &qfull_bar[s], kEvictLast);
         }
@@ -309,7 +318,9 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
 #pragma unroll
             for (int ks = 0; ks < BK / 8; ++ks) {
               const uint64_t adv = (uint64_t)(2 * ks);  // 32 bytes along K = +2 in the 16-byte address field
-              if (!(p.dbg & 2)) {
+              if (SCREEN) {  // one product: tf32(q - c) x tf32(x), both cut by the tensor core itself
+                umma_tf32_ss_pair(d_tmem, q_hi + adv, x_hi + adv, p.idesc, ks ? 1u : first);
+              } else if (!(p.dbg & 2)) {
                 umma_tf32_ss_pair(d_tmem, q_hi + adv, x_lo + adv, p.idesc, ks ? 1u : first);
                 umma_tf32_ss_pair(d_tmem, q_lo + adv, x_hi + adv, p.idesc, 1u);
                 umma_tf32_ss_pair(d_tmem, q_hi + adv, x_hi + adv, p.idesc, 1u);
@@ -366,12 +377,12 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             nn = fmaf(x[i].x, x[i].x, nn); nn = fmaf(x[i].y, x[i].y, nn);
             nn = fmaf(x[i].z, x[i].z, nn); nn = fmaf(x[i].w, x[i].w, nn);
             sx += (x[i].x + x[i].y) + (x[i].z + x[i].w);
-            if (!(p.dbg & 16)) {  // dbg 16 (with dbg 2): read-only converter, the probe of a screening pass
+            if (!SCREEN && !(p.dbg & 16)) {  // the screening pass only reads: |x|^2 and sum(x), no split tiles
               if (!(p.dbg & 8)) raw[c] = h;
               lo[c] = l;
             }
           }
-          if (!(p.dbg & 16)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+          if (!SCREEN && !(p.dbg & 16)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
         }
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(&conv_bar[s], 0);
@@ -403,7 +414,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     const int eh = warp >= 12 ? 1 : 0;
     const int tq = (warp & 3) * 32 + lane;
     const int q = (int)rank * BM + tq;
-    const bool valid = q < p.B;
+    const bool valid = q < p.B && (p.active_mask == nullptr || ((__ldcg(p.active_mask + (q >> 5)) >> (q & 31)) & 1u));
     const float qmean_r = valid ? p.q_mean[q] : 0.f;
     const float invq_r = valid ? p.inv_qn[q] : 0.f;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
@@ -535,10 +546,11 @@ bool qencode_x(void* fn, CUtensorMap* m, const float* base, long long rows, int 
              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 // the two planes written by k2_prepare (q_hi [B][q_ld] then q_lo [B][q_ld]) as ONE 3-D tensor
-bool qencode_q(void* fn, CUtensorMap* m, const float* planes, int B, int dim, int q_ld, int bk) {
-  const cuuint64_t gdim[3] = {(cuuint64_t)dim, (cuuint64_t)B, 2};
+// (planes == 1: the screening pass loads the q_hi plane only)
+bool qencode_q(void* fn, CUtensorMap* m, const float* planes, int B, int dim, int q_ld, int bk, int nplanes) {
+  const cuuint64_t gdim[3] = {(cuuint64_t)dim, (cuuint64_t)B, (cuuint64_t)nplanes};
   const cuuint64_t gstr[2] = {(cuuint64_t)q_ld * 4, (cuuint64_t)B * q_ld * 4};
-  const cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)BM, 2};
+  const cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)BM, (cuuint32_t)nplanes};
   const cuuint32_t estr[3] = {1, 1, 1};
   return reinterpret_cast<EncodeTiledFn>(fn)(
              m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(planes), gdim, gstr, box, estr,
@@ -548,10 +560,10 @@ bool qencode_q(void* fn, CUtensorMap* m, const float* planes, int B, int dim, in
 
 constexpr size_t kSmemCap = 227 * 1024;
 
-template <int BK>
+template <int BK, bool SCREEN>
 int qpick_stages(int k) {
   for (int s = kMaxStages; s >= 2; --s)
-    if ((size_t)qcarve<BK>(k, s).total + 1024 <= kSmemCap) return s;
+    if ((size_t)qcarve<BK, SCREEN>(k, s).total + 1024 <= kSmemCap) return s;
   return 0;
 }
 
@@ -570,7 +582,7 @@ int q_pairs(long long n, int num_sms) {
   return (int)(tiles2 < pairs ? (tiles2 < 1 ? 1 : tiles2) : pairs);
 }
 
-template <int BK>
+template <int BK, bool SCREEN>
 cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
   QDev p;
   p.n = a.n;
@@ -578,7 +590,7 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
   p.dim = a.dim;
   p.B = a.B;
   p.k = a.k;
-  p.stages = qpick_stages<BK>(a.k);
+  p.stages = qpick_stages<BK, SCREEN>(a.k);
   {
     const char* v = getenv("CSLAM_NNS_K2_STAGES");
     if (v && atoi(v) >= 2 && atoi(v) < p.stages) p.stages = atoi(v);
@@ -586,9 +598,14 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
     p.dbg = v ? atoi(v) : 0;
   }
   p.kblocks = (a.dim + BK - 1) / BK;
-  p.inv_qn = a.inv_qn;
-  p.q_mean = a.inv_qn + a.B;
-  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn + 2 * a.B));  // zeroed by k2_prepare
+  p.inv_qn = a.inv_qn + kQParInv * a.B;
+  p.q_mean = a.inv_qn + kQParMean * a.B;
+  // zeroed by k2_prepare; the masked fallback pass has its own plane (the screening pass's bounds are bounds
+  // of the SCREENED similarities and are still needed by k6_rescore's proof when the fallback runs)
+  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn)) +
+           (a.active_mask ? kQParGthrFull : kQParGthr) * a.B;
+  p.active_mask = a.active_mask;
+  p.active_count = a.active_count;
   p.part_keys = a.part_keys;
   // kind::tf32, fp32 accumulate, K-major operands; N>>3 at bit 17, M>>4 at bit 24 (M = 256 over the pair)
   p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN2 >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
@@ -598,16 +615,16 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
   }
   CUtensorMap mx, mq;
   if (!qencode_x(a.encode_fn, &mx, a.db, a.n, a.dim, a.ld, BK) ||
-      !qencode_q(a.encode_fn, &mq, a.q_lo, a.B, a.dim, a.q_ld, BK)) {
+      !qencode_q(a.encode_fn, &mq, a.q_lo, a.B, a.dim, a.q_ld, BK, SCREEN ? 1 : 2)) {
     if (err) *err = "k2: cuTensorMapEncodeTiled failed";
     return cudaErrorInvalidValue;
   }
-  const size_t smem = qcarve<BK>(p.k, p.stages).total + 1024;
+  const size_t smem = qcarve<BK, SCREEN>(p.k, p.stages).total + 1024;
   static bool attr_set[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(k2q_kernel<BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap);
+    cudaError_t e = cudaFuncSetAttribute(k2q_kernel<BK, SCREEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap);
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
@@ -620,7 +637,7 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
     cudaMemsetAsync(prof_buf, 0, 1024 * 16 * sizeof(u64), stream);
     p.prof = prof_buf;
   }
-  k2q_kernel<BK><<<grid, kThreads, smem, stream>>>(mx, mq, p);
+  k2q_kernel<BK, SCREEN><<<grid, kThreads, smem, stream>>>(mx, mq, p);
   count_launch();
   if (want_prof) {
     static u64 hbuf[1024 * 16];
@@ -666,7 +683,7 @@ int q_route(int B, int dim) {
 bool k2_supported(int B, int k, int dim) {
   if (B < 1 || B > kK2MaxBatch || k < 1 || k > 32) return false;
   switch (q_route(B, dim)) {
-    case 0: return (q_env_bk() == 16 ? qpick_stages<16>(k) : qpick_stages<32>(k)) >= 2;
+    case 0: return (q_env_bk() == 16 ? qpick_stages<16, false>(k) : qpick_stages<32, false>(k)) >= 2;
     default: return k2s_supported(B, k);
   }
 }
@@ -679,13 +696,23 @@ int k2_parts(long long n, int B, int dim, int num_sms) {
 }
 
 const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim) {
-  (void)dim;  // both kernels publish their bounds in the third plane
-  return reinterpret_cast<const unsigned*>(inv_qn + 2 * B);
+  (void)dim;  // both kernels publish their bounds in the same plane
+  return reinterpret_cast<const unsigned*>(inv_qn + kQParGthr * B);
+}
+
+// The screening route (one tf32 product + exact re-scoring, k6_rescore.cu) serves the batches the query-major
+// kernel serves.  CSLAM_NNS_SCREEN=0 switches it off (every batch then takes the 3xTF32 pass).
+bool k2_screen_supported(int B, int k, int dim) {
+  static const bool off = getenv("CSLAM_NNS_SCREEN") && atoi(getenv("CSLAM_NNS_SCREEN")) == 0;
+  if (off || B < 1 || B > kK2MaxBatch || k < 1 || k > 32 || q_env_bk() != 32) return false;
+  return q_route(B, dim) == 0 && qpick_stages<32, true>(k) >= 2;
 }
 
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {
   switch (q_route(a.B, a.dim)) {
-    case 0: return q_env_bk() == 16 ? qlaunch<16>(a, num_sms, stream, err) : qlaunch<32>(a, num_sms, stream, err);
+    case 0:
+      if (a.screen) return qlaunch<32, true>(a, num_sms, stream, err);
+      return q_env_bk() == 16 ? qlaunch<16, false>(a, num_sms, stream, err) : qlaunch<32, false>(a, num_sms, stream, err);
     default: return k2s_launch(a, num_sms, stream, err);
   }
 }

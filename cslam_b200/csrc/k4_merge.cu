@@ -20,9 +20,12 @@ constexpr int W4 = 4;
 __global__ void __launch_bounds__(W4 * 32) k4_kernel(const u64* __restrict__ keys, int parts,
                                                      long long B, int k_in, int k_out,
                                                      const unsigned* __restrict__ floor_ord,
+                                                     const unsigned* __restrict__ active_mask,
                                                      u64* out_keys, long long* out_idx,
                                                      float* out_sim, long long idx_stride,
                                                      long long idx_offset) {
+  // merge behind the masked fallback pass: only the queries that pass served have lists (and results to write)
+  if (active_mask != nullptr && !((__ldcg(active_mask + (blockIdx.x >> 5)) >> (blockIdx.x & 31)) & 1u)) return;
   extern __shared__ __align__(16) unsigned char smem4[];
   u64* lists = reinterpret_cast<u64*>(smem4);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -88,11 +91,12 @@ __global__ void __launch_bounds__(W4 * 32) k4_kernel(const u64* __restrict__ key
 
 cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_out, u64* out_keys,
                      long long* out_idx, float* out_sim, long long idx_stride,
-                     long long idx_offset, cudaStream_t stream, const unsigned* floor_ord) {
+                     long long idx_offset, cudaStream_t stream, const unsigned* floor_ord,
+                     const unsigned* active_mask) {
   if (B <= 0 || k_out <= 0) return cudaSuccess;
   const size_t smem = (size_t)W4 * k_out * 8;
-  k4_kernel<<<(unsigned)B, W4 * 32, smem, stream>>>(keys, parts, B, k_in, k_out, floor_ord, out_keys, out_idx,
-                                                    out_sim, idx_stride, idx_offset);
+  k4_kernel<<<(unsigned)B, W4 * 32, smem, stream>>>(keys, parts, B, k_in, k_out, floor_ord, active_mask, out_keys,
+                                                    out_idx, out_sim, idx_stride, idx_offset);
   count_launch();
   return cudaGetLastError();
 }

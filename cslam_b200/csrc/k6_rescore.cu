@@ -1,0 +1,257 @@
+// K6 — exact fp32 re-scoring of the screening pass's candidates, with a per-query completeness PROOF.
+//
+// The batched search needs fp32-faithful similarities (cslam/nns_matching.py:61), which on the tensor core costs
+// three tf32 products per K slice (3xTF32).  The screening pass (k2_qm.cu, SCREEN) runs ONE product,
+//     s~(x) = ( tf32(x) . tf32(q - c) + c * sum(x) ) / (max(|x|, eps) * max(|q|, eps)),
+// and keeps, per query, 2 * (SMs / 2) thread-private lists of the k best rows BY s~ plus the shared bound tau_q
+// every list publishes when it is full.  Two facts make an exact answer out of that:
+//
+//  (1) |s~(x) - s(x)| <= E_q for EVERY row x, s being the fp32 similarity this kernel computes.  The operands are
+//      cut to tf32 (relative error < 2^-10 each), so the dot product is off by at most
+//      (2^-9 + 2^-20) * sum_i |x_i| |q_i - c| <= 2^-9 |x| |q - c| (Cauchy-Schwarz); dividing by |x| |q| leaves
+//      2^-9 * rho_q, rho_q = |q - c| / |q| — independent of the row.  The remaining terms (fp32 accumulation in
+//      tensor memory, the converter's fp32 |x|^2 and sum(x), epilogue and re-scoring roundings) are bounded in
+//      k2_prepare, which writes E_q (x 1.25) next to the other per-query parameters.
+//  (2) Every row that is in NONE of the query's lists has s~ <= tau_q: a row is only ever dropped, or evicted
+//      from a list, against a full list's smallest entry or against the shared bound, and the shared bound at the
+//      end of the pass is >= every full list's smallest entry (offer_key publishes it whenever it grows).
+//
+// Per query (one CTA): take the k best candidates by s~ out of the union of the lists, re-score them exactly:
+// their smallest exact similarity L0 is a lower bound of the final k-th best.  Re-score every other candidate
+// with s~ >= L0 - E_q (the "band": by (1) nothing else in the union can reach L0).  If tau_q < L0 - E_q, by (1)
+// and (2) no row outside the union can reach L0 either, so the k best exact keys among the re-scored rows ARE
+// the exact top-k of the whole database: they are written out (sorted, lower row first on equal similarity,
+// like every other path).  Otherwise — tau_q too close (databases full of near-duplicates), more than kBandCap
+// rows in the band, NaN anywhere — the query's bit is set in the fallback mask and the masked 3xTF32 pass
+// queued right behind this kernel recomputes it; that pass exits at once when no bit is set.
+//
+// Latency-bound: B * (k + band) rows of ld * 4 bytes (C3: 256 x ~40 x 16 KB = 170 MB, ~1 % of the pass).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace cslam {
+namespace {
+
+constexpr int W6 = 8;            // warps per CTA
+constexpr int kBandCap = 224;    // rows beyond the screened top-k one query may re-score before giving up
+constexpr int kMaxExact = 32 + kBandCap;
+
+struct K6Dev {
+  const float* db;
+  long long n;
+  int ld, dim;
+  const float* q;
+  int q_ld;
+  const float* inv_qn;
+  const float* ebound;
+  const unsigned* gthr;
+  const u64* part_keys;
+  int parts, B, k;
+  u64* out_keys;
+  long long* out_idx;
+  float* out_sim;
+  long long idx_stride, idx_offset;
+  unsigned* fail_mask;
+  unsigned* fail_count;
+  unsigned long long* stats;
+};
+
+__device__ __forceinline__ void fma4x(const float4& x, const float4& q, float& dot, float& nn) {
+  dot = fmaf(x.x, q.x, dot);
+  dot = fmaf(x.y, q.y, dot);
+  dot = fmaf(x.z, q.z, dot);
+  dot = fmaf(x.w, q.w, dot);
+  nn = fmaf(x.x, x.x, nn);
+  nn = fmaf(x.y, x.y, nn);
+  nn = fmaf(x.z, x.z, nn);
+  nn = fmaf(x.w, x.w, nn);
+}
+
+// fp32 cosine similarity of one database row with the query, computed by a whole warp; the same formula as
+// the single-query kernel: x.q * rsqrt(max(|x|^2, eps^2)) * (1 / max(|q|, eps))   (nns_matching.py:61)
+__device__ __forceinline__ float warp_exact_sim(const float* __restrict__ row, const float* __restrict__ q,
+                                                int dim, float inv_qn, int lane) {
+  const float4* r4 = reinterpret_cast<const float4*>(row);
+  const float4* q4 = reinterpret_cast<const float4*>(q);
+  const int full4 = dim >> 2;  // float4s that lie entirely inside the descriptor
+  float d0 = 0.f, n0 = 0.f, d1 = 0.f, n1 = 0.f, d2 = 0.f, n2 = 0.f, d3 = 0.f, n3 = 0.f;
+  int j = lane;
+  for (; j + 96 < full4; j += 128) {
+    const float4 x0 = __ldg(r4 + j), x1 = __ldg(r4 + j + 32), x2 = __ldg(r4 + j + 64), x3 = __ldg(r4 + j + 96);
+    const float4 y0 = __ldg(q4 + j), y1 = __ldg(q4 + j + 32), y2 = __ldg(q4 + j + 64), y3 = __ldg(q4 + j + 96);
+    fma4x(x0, y0, d0, n0);
+    fma4x(x1, y1, d1, n1);
+    fma4x(x2, y2, d2, n2);
+    fma4x(x3, y3, d3, n3);
+  }
+  for (; j < full4; j += 32) fma4x(__ldg(r4 + j), __ldg(q4 + j), d0, n0);
+  if (lane == 0) {  // the last, partial float4 of a dim that is not a multiple of 4 (the query's pad is not ours)
+    for (int i = full4 * 4; i < dim; ++i) {
+      const float x = __ldg(row + i);
+      d1 = fmaf(x, __ldg(q + i), d1);
+      n1 = fmaf(x, x, n1);
+    }
+  }
+  float dot = (d0 + d1) + (d2 + d3), nn = (n0 + n1) + (n2 + n3);
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    dot += __shfl_xor_sync(kFull, dot, off);
+    nn += __shfl_xor_sync(kFull, nn, off);
+  }
+  return dot * rsqrtf(fmaxf(nn, kEps * kEps)) * inv_qn;
+}
+
+__global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
+  extern __shared__ __align__(16) unsigned char smem6[];
+  u64* keys = reinterpret_cast<u64*>(smem6);  // the union of this query's lists: [parts * k]
+  __shared__ u64 wl[W6 * 32];                 // per-warp top-k by s~
+  __shared__ u64 topk[32];                    // the k best candidates by s~, descending
+  __shared__ u64 exact[kMaxExact];            // exact keys of everything re-scored
+  __shared__ u64 band[kBandCap];
+  __shared__ u64 outk[32];
+  __shared__ float exs[32];
+  __shared__ int band_cnt, bad;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x, k = p.k;
+  const int total = p.parts * k;
+  if (tid == 0) {
+    band_cnt = 0;
+    bad = 0;
+    if (b == 0 && p.stats) atomicAdd(p.stats, (unsigned long long)p.B);
+  }
+  if (tid < 32) {
+    outk[tid] = 0ull;
+    exs[tid] = 0.f;
+  }
+  __syncthreads();
+
+  // ---- 1. the union of the lists -> shared memory; its k best keys by s~ -------------------------------------
+  u64 thr = 0ull, mine = 0ull;
+  int saw_nan = 0;
+  for (int base = 0; base < total; base += W6 * 32) {
+    const int i = base + tid;
+    u64 key = 0ull;
+    if (i < total) {
+      const int part = i / k, j = i - part * k;
+      key = __ldcg(p.part_keys + ((size_t)part * p.B + b) * k + j);
+      keys[i] = key;
+      saw_nan |= ((unsigned)(key >> 32) == 0xffffffffu);
+    }
+    offer(nullptr, k, key, key != 0ull, thr, mine, lane);
+  }
+  if (k == 1) mine = lane == 0 ? thr : 0ull;  // offer() keeps the k == 1 winner in `thr`
+  wl[warp * 32 + lane] = lane < k ? mine : 0ull;
+  if (saw_nan) bad = 1;  // NaN similarities sort first in the reference: left to the 3xTF32 pass
+  __syncthreads();
+  if (warp == 0) {
+    u64 v = wl[lane];
+#pragma unroll
+    for (int w = 1; w < W6; ++w) v = warp_merge_desc(v, wl[w * 32 + lane], lane);
+    topk[lane] = lane < k ? v : 0ull;
+  }
+  __syncthreads();
+  int m_top = 0;
+  for (int j = 0; j < k; ++j) m_top += topk[j] != 0ull;
+  const float* q = p.q + (size_t)b * p.q_ld;
+  const float inv_qn = p.inv_qn[b];
+
+  // ---- 2. exact similarities of those k rows: the smallest one, L0, bounds the final k-th best from below ------
+  for (int j = warp; j < m_top; j += W6) {
+    const uint32_t row = key_row(topk[j]);
+    const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
+    if (lane == 0) {
+      exact[j] = make_key(s, row);
+      exs[j] = s;
+    }
+  }
+  __syncthreads();
+  float l0 = INFINITY;
+  for (int j = 0; j < m_top; ++j) l0 = fminf(l0, exs[j]);  // fminf skips NaN: checked separately below
+  bool nan_exact = false;
+  for (int j = 0; j < m_top; ++j) nan_exact |= !(exs[j] == exs[j]);
+  const float E = p.ebound[b];
+  const float lim = l0 - E;
+  const u64 kth = m_top > 0 ? topk[m_top - 1] : 0ull;
+
+  // ---- 3. the band: every other candidate whose screened similarity could still reach L0 -------------------------
+  for (int i = tid; i < total; i += W6 * 32) {
+    const u64 key = keys[i];
+    if (key != 0ull && key < kth && key_sim(key) >= lim) {
+      const int at = atomicAdd(&band_cnt, 1);
+      if (at < kBandCap) band[at] = key;
+    }
+  }
+  __syncthreads();
+  const int nband = band_cnt;
+  const int m = nband < kBandCap ? nband : kBandCap;
+  for (int j = warp; j < m; j += W6) {
+    const uint32_t row = key_row(band[j]);
+    const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
+    if (lane == 0) {
+      exact[m_top + j] = make_key(s, row);
+      if (!(s == s)) bad = 1;
+    }
+  }
+  __syncthreads();
+
+  // ---- 4. the proof, or the fallback -------------------------------------------------------------------------------
+  const unsigned g = __ldcg(p.gthr + b);
+  // g == 0: no list ever filled up, nothing was dropped anywhere: the union is the whole database
+  const bool outside_ok = g == 0u || (ord_to_sim(g) < lim);
+  const bool proven = !bad && !nan_exact && m_top == k && nband <= kBandCap && outside_ok && (lim == lim);
+  if (!proven) {
+    if (tid == 0) {
+      atomicOr(p.fail_mask + (b >> 5), 1u << (b & 31));
+      atomicAdd(p.fail_count, 1u);
+      if (p.stats) atomicAdd(p.stats + 1, 1ull);
+    }
+    return;
+  }
+  block_rank_select(exact, m_top + m, k, outk);
+  __syncthreads();
+  if (tid < k) {
+    const u64 key = outk[tid];
+    const bool have = key != 0ull;
+    const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
+    const size_t o = (size_t)b * k + tid;
+    if (p.out_keys) p.out_keys[o] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
+    if (p.out_idx) p.out_idx[o] = have ? grow : -1ll;
+    if (p.out_sim) p.out_sim[o] = have ? key_sim(key) : -INFINITY;
+  }
+}
+
+}  // namespace
+
+cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
+  if (a.B <= 0 || a.k <= 0 || a.k > 32) return cudaErrorInvalidValue;
+  K6Dev p;
+  p.db = a.db;
+  p.n = a.n;
+  p.ld = a.ld;
+  p.dim = a.dim;
+  p.q = a.q;
+  p.q_ld = a.q_ld;
+  p.inv_qn = a.qpar + kQParInv * a.B;
+  p.ebound = a.qpar + kQParEbound * a.B;
+  p.gthr = reinterpret_cast<const unsigned*>(a.qpar) + kQParGthr * a.B;
+  p.part_keys = a.part_keys;
+  p.parts = a.parts;
+  p.B = a.B;
+  p.k = a.k;
+  p.out_keys = a.out_keys;
+  p.out_idx = a.out_idx;
+  p.out_sim = a.out_sim;
+  p.idx_stride = a.idx_stride;
+  p.idx_offset = a.idx_offset;
+  unsigned* tail = reinterpret_cast<unsigned*>(const_cast<float*>(a.qpar)) + kQParPlanes * a.B;
+  p.fail_mask = tail;
+  p.fail_count = tail + 8;
+  p.stats = a.stats;
+  const size_t smem = (size_t)a.parts * a.k * 8;
+  if (smem > 40 * 1024) return cudaErrorInvalidConfiguration;
+  k6_kernel<<<(unsigned)a.B, W6 * 32, smem, stream>>>(p);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace cslam

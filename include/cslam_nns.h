@@ -203,6 +203,15 @@ int cslam_nns_search_sharded(cslam_nns_t h, cslam_nns_xchg_t x, const float* que
 int cslam_nns_set_variant(cslam_nns_t h, int variant);
 /* Variant actually used by the last search on this handle (1, 2 or 3; 0 = none yet). */
 int cslam_nns_last_variant(cslam_nns_t h);
+/* Screening route of the batched search (variant 2, batches the query-major kernel serves): one tf32 product
+ * over the database, exact fp32 re-scoring of each query's candidates with a completeness proof, the 3xTF32 pass
+ * only for the queries the proof does not cover.  Results obey the same parity rule either way.  enable = 0
+ * makes every batch take the 3xTF32 pass; min_rows (>= 0) is the smallest database that is screened (-1 keeps
+ * the current value, default 8192).  Environment: CSLAM_NNS_SCREEN=0, CSLAM_NNS_SCREEN_MIN_ROWS. */
+int cslam_nns_set_screen(cslam_nns_t h, int enable, int64_t min_rows);
+/* Counters since the handle was created: queries that went through the screening pass, and how many of them the
+ * proof did not cover (recomputed by the 3xTF32 pass).  Synchronises the device. */
+int cslam_nns_screen_stats(cslam_nns_t h, int64_t* screened, int64_t* fallback);
 /* Time in milliseconds (CUDA events on `stream`) of `iters` back-to-back device-resident searches of
  * the same query block: the kernel-only figure the roofline is computed from.  queries_dev is device
  * memory; results are discarded.  Returns the per-search average in *ms_per_search. */

@@ -444,7 +444,7 @@ def test_save_load_refuses_pickle_by_default_and_data_setter(M, tmp_path):
 
 # ---- both batched tilings on every shape --------------------------------------------------------------
 
-@pytest.mark.parametrize("route", ["qm", "rows"])
+@pytest.mark.parametrize("route", ["qm", "rows", "qm_noscreen", "qm_screen_all"])
 def test_both_batched_kernels_on_all_shapes(route):
     """The router (k2_qm.cu: q_route) normally sends small batches (<= 96 queries, fewer at small
     dimensions) to the row-major kernel and the rest to the query-major CTA-pair kernel; here each kernel is forced (the switch is read once per process,
@@ -458,7 +458,11 @@ def test_both_batched_kernels_on_all_shapes(route):
     if route == "rows":   # the row-major kernel holds <= 192 queries (tensor-memory columns); larger forced
         # batches fall through to the query-major kernel, which the other parameter covers
         shapes = [s for s in shapes if int(s.split(",")[2]) <= 192] + ["9000,96,192,4", "2500,72,130,32"]
-    env = dict(os.environ, CSLAM_NNS_K2_FORCE=route)
+    env = dict(os.environ, CSLAM_NNS_K2_FORCE=route.split("_")[0])
+    if route == "qm_noscreen":      # every batch through the 3xTF32 pass, also the big databases
+        env["CSLAM_NNS_SCREEN"] = "0"
+    elif route == "qm_screen_all":  # the screening route (one product + exact re-scoring) on EVERY shape,
+        env["CSLAM_NNS_SCREEN_MIN_ROWS"] = "0"   # also n < 256, k = 32, dim not a multiple of 4 or 32
     out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "k2_check.py")] + shapes, env=env,
                          capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "K2 CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
