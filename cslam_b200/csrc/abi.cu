@@ -1,5 +1,6 @@
 // C-ABI of the matcher (include/cslam_nns.h).  Host-side logic only: storage, staging, variant
 // dispatch.  The arithmetic is in k1_single.cu / k2_batched.cu / k3_sort.cu / k4_merge.cu.
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -132,6 +133,21 @@ int fail_cuda(cslam_nns_t h, const char* what, cudaError_t e) {
   do {                                                \
     cudaError_t e__ = (call);                         \
     if (e__ != cudaSuccess) return fail_cuda(h, #call, e__); \
+  } while (0)
+
+// CSLAM_NNS_DEBUG_SYNC=1: synchronise after every launch of the batched route and name the kernel that faulted
+// (compute-sanitizer is not available on every pool; this is the poor man's bisect)
+int debug_sync(cslam_nns_t h, cudaStream_t stream, const char* what) {
+  static const bool on = env_int("CSLAM_NNS_DEBUG_SYNC", 0) != 0;
+  if (!on) return 0;
+  cudaError_t e = cudaStreamSynchronize(stream);
+  if (e != cudaSuccess) return fail_cuda(h, what, e);
+  return 0;
+}
+#define DBG_SYNC(h, stream, what)                  \
+  do {                                             \
+    int rc__ = debug_sync(h, stream, what);        \
+    if (rc__) return rc__;                         \
   } while (0)
 
 int grow_to(cslam_nns_t h, long long rows, cudaStream_t stream) {
@@ -315,11 +331,14 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
   for (long long b0 = 0; b0 < B; b0 += kK2MaxBatch) {
     const int Bc = (int)((B - b0) > kK2MaxBatch ? kK2MaxBatch : (B - b0));
     const int grid = k2_parts(h->n, Bc, h->dim, h->num_sms);
+    const bool screen = h->screen && h->n >= h->screen_min_rows && k2_screen_supported(Bc, k_run, (int)h->dim);
+    const int kl = screen ? k2_screen_list_len(k_run) : k_run;   // list capacity of the first pass
     if (!h->q_lo.ensure((size_t)2 * Bc * q_ld * 4) || !h->inv_qn.ensure(k2_qpar_bytes(Bc)) ||
-        !h->part_keys.ensure((size_t)grid * Bc * k_run * 8))
+        !h->part_keys.ensure((size_t)grid * Bc * kl * 8))
       return fail(h, CSLAM_NNS_ENOMEM, "batched scratch");
     const float* qc = dq + b0 * q_ld;
     CK(h, k2_prepare(qc, Bc, (int)h->dim, (int)q_ld, (float*)h->q_lo.p, (float*)h->inv_qn.p, stream));
+    DBG_SYNC(h, stream, "after k2_prepare");
     K2Args a;
     a.db = (const float*)h->arena.base();
     a.n = h->n;
@@ -342,18 +361,19 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
     // fp32 re-scoring of the few candidates per query with a completeness proof (k6_rescore.cu), and the 3xTF32
     // pass only for the queries the proof does not cover — queued unconditionally, it exits at once when there
     // are none, so the call stays stream-ordered without a host round trip.
-    const bool screen = h->screen && h->n >= h->screen_min_rows && k2_screen_supported(Bc, k_run, (int)h->dim);
     if (screen) {
       if (!h->screen_stats.p) {
         if (!h->screen_stats.ensure(16)) return fail(h, CSLAM_NNS_ENOMEM, "screening counters");
         CK(h, cudaMemsetAsync(h->screen_stats.p, 0, 16, stream));
       }
       a.screen = true;
+      a.k = kl;
       {
         KernelTimer kt(h, stream);
         e = k2_launch(a, h->num_sms, stream, &kerr);
       }
       if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (screening)", e);
+      DBG_SYNC(h, stream, "after the screening kernel");
       K6Args r;
       r.db = a.db;
       r.n = a.n;
@@ -366,6 +386,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       r.parts = grid;
       r.B = Bc;
       r.k = k_run;
+      r.kl = kl;
       r.out_keys = ok_;
       r.out_idx = oi_;
       r.out_sim = os_;
@@ -373,14 +394,18 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       r.idx_offset = idx_offset;
       r.stats = (unsigned long long*)h->screen_stats.p;
       CK(h, k6_rescore(r, stream));
+      DBG_SYNC(h, stream, "after k6_rescore");
       const unsigned* tail = (const unsigned*)h->inv_qn.p + (size_t)kQParPlanes * Bc;
       a.screen = false;
+      a.k = k_run;
       a.active_mask = tail;
       a.active_count = tail + 8;
       e = k2_launch(a, h->num_sms, stream, &kerr);
       if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (fallback)", e);
+      DBG_SYNC(h, stream, "after the fallback kernel");
       CK(h, k4_merge((const u64*)h->part_keys.p, grid, Bc, k_run, k_run, ok_, oi_, os_, idx_stride, idx_offset,
                      stream, (const unsigned*)h->inv_qn.p + (size_t)kQParGthrFull * Bc, tail));
+      DBG_SYNC(h, stream, "after the fallback merge");
       continue;
     }
     {

@@ -705,7 +705,20 @@ const unsigned* k2_floor_plane(const float* inv_qn, int B, int dim) {
 bool k2_screen_supported(int B, int k, int dim) {
   static const bool off = getenv("CSLAM_NNS_SCREEN") && atoi(getenv("CSLAM_NNS_SCREEN")) == 0;
   if (off || B < 1 || B > kK2MaxBatch || k < 1 || k > 32 || q_env_bk() != 32) return false;
-  return q_route(B, dim) == 0 && qpick_stages<32, true>(k) >= 2;
+  return q_route(B, dim) == 0 && qpick_stages<32, true>(k2_screen_list_len(k)) >= 2;
+}
+
+// Lists of the screening pass hold more than k entries: 2k + 4, at least 12, at most 32 (k = 1 -> 12, 10 -> 24,
+// >= 14 -> 32).  See k6_rescore.cu: the spare entries keep the published bound below the k-th best when a
+// query's neighbours all fall into one list.  Larger lists cost shared memory (ring depth 6 -> 4 stages at 32),
+// not time: insertions are warm-up work.  CSLAM_NNS_SCREEN_LIST overrides (development).
+int k2_screen_list_len(int k) {
+  static const int forced = getenv("CSLAM_NNS_SCREEN_LIST") ? atoi(getenv("CSLAM_NNS_SCREEN_LIST")) : 0;
+  int kl = forced > 0 ? forced : 2 * k + 4;
+  if (forced <= 0 && kl < 12) kl = 12;
+  if (kl < k) kl = k;
+  if (kl > 32) kl = 32;
+  return kl;
 }
 
 cudaError_t k2_launch(const K2Args& a, int num_sms, cudaStream_t stream, const char** err) {

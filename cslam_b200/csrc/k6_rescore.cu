@@ -3,8 +3,11 @@
 // The batched search needs fp32-faithful similarities (cslam/nns_matching.py:61), which on the tensor core costs
 // three tf32 products per K slice (3xTF32).  The screening pass (k2_qm.cu, SCREEN) runs ONE product,
 //     s~(x) = ( tf32(x) . tf32(q - c) + c * sum(x) ) / (max(|x|, eps) * max(|q|, eps)),
-// and keeps, per query, 2 * (SMs / 2) thread-private lists of the k best rows BY s~ plus the shared bound tau_q
-// every list publishes when it is full.  Two facts make an exact answer out of that:
+// and keeps, per query, 2 * (SMs / 2) thread-private lists of the kl >= k best rows BY s~ plus the shared bound
+// tau_q every list publishes when it is full.  (kl > k matters: the list that holds the query's true neighbours
+// — consecutive keyframes of a revisited place sit in consecutive rows, hence in ONE list — would otherwise
+// evict rows right below its k-th entry and publish a bound right at the k-th best; with kl - k spare entries
+// the bound sits kl - k candidates lower.)  Two facts make an exact answer out of that:
 //
 //  (1) |s~(x) - s(x)| <= E_q for EVERY row x, s being the fp32 similarity this kernel computes.  The operands are
 //      cut to tf32 (relative error < 2^-10 each), so the dot product is off by at most
@@ -54,6 +57,7 @@ struct K6Dev {
   unsigned* fail_mask;
   unsigned* fail_count;
   unsigned long long* stats;
+  int kl;  // capacity of the screening pass's lists (>= k)
 };
 
 __device__ __forceinline__ void fma4x(const float4& x, const float4& q, float& dot, float& nn) {
@@ -112,8 +116,8 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   __shared__ float exs[32];
   __shared__ int band_cnt, bad;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.x, k = p.k;
-  const int total = p.parts * k;
+  const int b = blockIdx.x, k = p.k, kl = p.kl;
+  const int total = p.parts * kl;
   if (tid == 0) {
     band_cnt = 0;
     bad = 0;
@@ -132,8 +136,8 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     const int i = base + tid;
     u64 key = 0ull;
     if (i < total) {
-      const int part = i / k, j = i - part * k;
-      key = __ldcg(p.part_keys + ((size_t)part * p.B + b) * k + j);
+      const int part = i / kl, j = i - part * kl;
+      key = __ldcg(p.part_keys + ((size_t)part * p.B + b) * kl + j);
       keys[i] = key;
       saw_nan |= ((unsigned)(key >> 32) == 0xffffffffu);
     }
@@ -158,6 +162,10 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   // ---- 2. exact similarities of those k rows: the smallest one, L0, bounds the final k-th best from below ------
   for (int j = warp; j < m_top; j += W6) {
     const uint32_t row = key_row(topk[j]);
+    if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
+      if (lane == 0) { exact[j] = 0ull; exs[j] = 0.f; bad = 1; }
+      continue;
+    }
     const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
     if (lane == 0) {
       exact[j] = make_key(s, row);
@@ -186,6 +194,10 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   const int m = nband < kBandCap ? nband : kBandCap;
   for (int j = warp; j < m; j += W6) {
     const uint32_t row = key_row(band[j]);
+    if ((long long)row >= p.n) {
+      if (lane == 0) { exact[m_top + j] = 0ull; bad = 1; }
+      continue;
+    }
     const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
     if (lane == 0) {
       exact[m_top + j] = make_key(s, row);
@@ -223,7 +235,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
 }  // namespace
 
 cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
-  if (a.B <= 0 || a.k <= 0 || a.k > 32) return cudaErrorInvalidValue;
+  if (a.B <= 0 || a.k <= 0 || a.k > 32 || a.kl < a.k || a.kl > 32) return cudaErrorInvalidValue;
   K6Dev p;
   p.db = a.db;
   p.n = a.n;
@@ -247,7 +259,8 @@ cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
   p.fail_mask = tail;
   p.fail_count = tail + 8;
   p.stats = a.stats;
-  const size_t smem = (size_t)a.parts * a.k * 8;
+  p.kl = a.kl;
+  const size_t smem = (size_t)a.parts * a.kl * 8;
   if (smem > 40 * 1024) return cudaErrorInvalidConfiguration;
   k6_kernel<<<(unsigned)a.B, W6 * 32, smem, stream>>>(p);
   count_launch();

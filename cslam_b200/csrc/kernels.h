@@ -57,6 +57,8 @@ cudaError_t k4_merge(const u64* keys, int parts, long long B, int k_in, int k_ou
                      const unsigned* active_mask = nullptr);
 // whether the batched search of B queries may take the screening route (query-major tiling, k2_qm.cu)
 bool k2_screen_supported(int B, int k, int dim);
+// capacity of the screening pass's per-thread lists for a top-k search (>= k, <= 32)
+int k2_screen_list_len(int k);
 
 // ---- K6: exact fp32 re-scoring of the screening pass's candidates, with the completeness proof (k6_rescore.cu)
 struct K6Args {
@@ -66,8 +68,9 @@ struct K6Args {
   const float* q;        // raw fp32 queries [B][q_ld]
   int q_ld;
   const float* qpar;     // the k2_prepare parameter block
-  const u64* part_keys;  // [parts][B][k] lists of the screening pass
+  const u64* part_keys;  // [parts][B][kl] lists of the screening pass
   int parts, B, k;
+  int kl;                // capacity of those lists, k <= kl <= 32
   u64* out_keys;
   long long* out_idx;
   float* out_sim;

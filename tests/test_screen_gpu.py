@@ -46,11 +46,12 @@ def test_screened_search_vs_oracle(n, d, B, k, dist):
         msg = oracle.check_parity(db, qs[j], k, idx[j], sims[j])
         assert msg is None, (j, msg)
     assert np.all(sims[:, :-1] >= sims[:, 1:])
-    # the re-scored similarities are plain fp32 dot products: far inside the tolerance
-    s64 = np.stack([oracle.cosine_similarities(db[idx[j]], qs[j], np.float64) for j in range(0, B, 7)])
-    assert np.abs(sims[::7] - s64).max() < 1e-6
-    if dist == "rand" and n >= 9000:
+    if n >= 9000:
         assert fallback <= B // 8, (screened, fallback)     # generic data: the proof covers (nearly) every query
+    # the re-scored similarities are plain fp32 dot products, far inside the tolerance (the 3xTF32 pass that
+    # answers the queries the proof does not cover is an order of magnitude less precise, still inside it)
+    s64 = np.stack([oracle.cosine_similarities(db[idx[j]], qs[j], np.float64) for j in range(0, B, 7)])
+    assert np.abs(sims[::7] - s64).max() < (1e-6 if fallback == 0 else 8e-6)
     # same rows as the 3xTF32 pass wherever the oracle sees no tie
     m._h.lib.cslam_nns_set_screen(m._h.h, 0, -1)
     idx3, sims3 = m._search_block(torch.from_numpy(qs), k)
@@ -60,6 +61,49 @@ def test_screened_search_vs_oracle(n, d, B, k, dist):
     for j, i in zip(*np.nonzero(differ)):
         a = oracle.cosine_similarities(db[[idx[j, i], idx3[j, i]]], qs[j], np.float64)
         assert abs(a[0] - a[1]) <= 1e-5 * abs(a[0]) + 1e-6
+
+
+def test_neighbours_in_consecutive_rows_are_proven_without_fallback():
+    """SLAM data: the keyframes of a revisited place are consecutive rows, i.e. they all land in ONE of the
+    screening pass's lists.  The lists hold 2k + 4 entries so that this does not push the list's published
+    bound up to the k-th best (which would send the query to the 3xTF32 pass every time)."""
+    n, d, B, k = 30000, 128, 128, 10
+    db = synth.unit_rows(83, n, d)
+    qs = synth.unit_rows(84, B, d)
+    eps = synth.normal(85, (B, 9, d)).astype(np.float32)
+    for j in range(B):                       # query j revisits a place seen at rows 200 j + 100 .. + 108
+        for t in range(9):
+            v = qs[j] + (0.03 + 0.01 * t) * eps[j, t]
+            db[200 * j + 100 + t] = v / np.linalg.norm(v)
+    m = _matcher(db)
+    idx, sims = m._search_block(torch.from_numpy(qs), k)
+    screened, fallback = _stats(m)
+    assert screened == B and fallback == 0, (screened, fallback)
+    for j in range(B):
+        assert sorted(idx[j][:9].tolist()) == list(range(200 * j + 100, 200 * j + 109))
+        msg = oracle.check_parity(db, qs[j], k, idx[j], sims[j])
+        assert msg is None, (j, msg)
+
+
+def test_screened_search_soak():
+    """Many screened searches back to back with changing batch sizes, k and databases: every call must agree
+    with the single-query kernel (same rows; similarities to fp32 rounding)."""
+    from cslam_b200 import NearestNeighborsMatching
+    for rep, (n, d) in enumerate([(9000, 100), (20000, 256), (33000, 48)]):
+        db = synth.unit_rows(600 + rep, n, d)
+        m = NearestNeighborsMatching()
+        m.add_items(db, list(range(n)))
+        m._h.lib.cslam_nns_set_screen(m._h.h, 1, 0)
+        for it, (B, k) in enumerate([(130, 10), (256, 1), (97, 5), (200, 16), (256, 10), (128, 32), (255, 3)] * 3):
+            qs = synth.queries_for(700 + 10 * rep + it, db, B)
+            idx, sims = m._search_block(torch.from_numpy(qs), k)
+            m._h.lib.cslam_nns_set_variant(m._h.h, 1)
+            sub = list(range(0, B, 16))
+            i1, s1 = m._search_block(torch.from_numpy(qs[sub]), k)
+            m._h.lib.cslam_nns_set_variant(m._h.h, 0)
+            np.testing.assert_allclose(sims[sub], s1, rtol=1e-5, atol=2e-6)
+            assert (idx[sub] == i1).mean() > 0.98
+        assert _stats(m)[0] > 0
 
 
 def test_near_duplicate_database_takes_the_fallback_and_stays_exact():
