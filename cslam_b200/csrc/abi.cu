@@ -101,6 +101,16 @@ struct cslam_nns_s {
   long long ids_synced = 0;  // rows [0, ids_synced) of ids_host are in ids_arena
   // optional per-kernel timing (cslam_nns_profile)
   cudaEvent_t add_ev = nullptr;  // completion of an append whose host source is pinned (cslam_nns_add)
+  // chained single-query searches of this database (programmatic dependent launch, k1_single.cu)
+  unsigned k1_seq = 0;             // ticket / scratch slot of the next launch = k1_seq % kK1Slots
+  bool k1_chain = false;           // the last thing this handle queued on k1_stream was a single-query search
+  cudaStream_t k1_stream = nullptr;
+  bool chain_enabled = true;       // CSLAM_NNS_CHAIN=0 switches the chaining off
+  bool data_exposed = false;       // cslam_nns_data_ptr was called: rows may change behind the library's back
+  // host-destination fast path: the kernel publishes a sequence number in mapped memory, the host spins on it
+  PinBuf done_host;
+  unsigned done_seq = 0;
+  bool want_done = false;
   bool profile = false;
   std::vector<cudaEvent_t> ev;   // pairs
   size_t ev_used = 0;
@@ -268,11 +278,19 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
     if (!h->ticket.ensure(64)) return fail(h, CSLAM_NNS_ENOMEM, "scratch allocation failed");
     CK(h, cudaMemsetAsync(h->ticket.p, 0, 64, stream));  // the kernels leave it at zero again
   }
-  if (!h->scratch.ensure((size_t)k1_max_grid(h->num_sms) * kK1MaxK * 8))
+  const size_t scratch_slot = (size_t)k1_max_grid(h->num_sms) * kK1MaxK;   // keys per ticket / scratch slot
+  if (!h->scratch.ensure(scratch_slot * kK1Slots * 8))
     return fail(h, CSLAM_NNS_ENOMEM, "scratch allocation failed");
+  if (variant != 1) h->k1_chain = false;
 
   if (variant == 1) {
     for (long long b = 0; b < B; ++b) {
+      // Every launch takes the next ticket / scratch slot of a ring of kK1Slots, so that a search chained behind
+      // the previous search of this database (same stream, nothing of ours queued in between, rows not exposed
+      // through cslam_nns_data_ptr) may be scheduled while that one is still finishing.
+      const unsigned slot = h->k1_seq++ % kK1Slots;
+      const bool same_db = h->k1_chain && h->k1_stream == stream && h->chain_enabled && !h->data_exposed &&
+                           !h->profile;
       K1Args a;
       a.db = (const float*)h->arena.base();
       a.n = h->n;
@@ -280,17 +298,25 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       a.dim = (int)h->dim;
       a.q = dq + b * q_ld;
       a.k = k_run;
-      a.scratch = (u64*)h->scratch.p;
-      a.ticket = (unsigned*)h->ticket.p;
+      a.scratch = (u64*)h->scratch.p + scratch_slot * slot;
+      a.ticket = (unsigned*)h->ticket.p + 4 * slot;   // 16 bytes per slot: ticket word, pad, best key
       a.out_keys = o_keys ? o_keys + b * k_run : nullptr;
       a.out_idx = o_idx ? o_idx + b * k_run : nullptr;
       a.out_sim = o_sim ? o_sim + b * k_run : nullptr;
       a.idx_stride = idx_stride;
       a.idx_offset = idx_offset;
       a.all_sims = nullptr;
-      a.overlap_prev = overlap_prev && B == 1 && !h->profile;
+      const bool other_db = overlap_prev && B == 1 && !h->profile;   // cslam_nns_search_multi: independent databases
+      a.overlap_prev = other_db || same_db;
+      a.dep_wait = !other_db && same_db;
+      if (h->want_done && b == B - 1 && k_run <= 32) {
+        a.done_flag = (unsigned*)h->done_host.p;
+        a.done_value = ++h->done_seq;
+      }
       KernelTimer kt(h, stream);
       CK(h, k1_launch(a, h->k1, h->num_sms, stream));
+      h->k1_chain = true;
+      h->k1_stream = stream;
     }
     return 0;
   }
@@ -419,6 +445,24 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
   return 0;
 }
 
+// Host side of the sequence-word handshake (k1_single.cu: done_flag): spin on the mapped word the last CTA writes
+// after the results, instead of a stream synchronisation (~8 us cheaper per synchronous single-query search).
+// The stream is polled now and then so that a faulted kernel ends the wait with its error.
+cudaError_t wait_done(cslam_nns_t h, unsigned want, cudaStream_t stream) {
+  volatile unsigned* flag = (volatile unsigned*)h->done_host.p;
+  for (unsigned it = 1;; ++it) {
+    if (*flag == want) return cudaSuccess;
+    if ((it & 0x3fff) == 0) {
+      const cudaError_t e = cudaStreamQuery(stream);
+      if (e != cudaErrorNotReady) return e;   // finished (flag or not), or failed
+      cudaGetLastError();
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+}
+
 // Bring the queries to device memory with a 16-byte aligned pitch (multiple of 4 floats).
 int stage_queries(cslam_nns_t h, const float* queries, long long B, long long q_ld, int src_is_device,
                   cudaStream_t stream, const float** dq, long long* dq_ld) {
@@ -481,6 +525,7 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->k1.stages = env_int("CSLAM_K1_STAGES", 2);  // 8 KB x 2 per warp: best of the B200 sweep (profiles/r1_k1_sweep_v2.log)
   h->k1.ctas = env_int("CSLAM_K1_CTAS", 0);
   h->variant = env_int("CSLAM_NNS_VARIANT", 0);
+  h->chain_enabled = env_int("CSLAM_NNS_CHAIN", 1) != 0;
   h->screen = env_int("CSLAM_NNS_SCREEN", 1) != 0;
   h->screen_min_rows = env_int("CSLAM_NNS_SCREEN_MIN_ROWS", 8192);
   *out = h;
@@ -511,6 +556,7 @@ int cslam_nns_destroy(cslam_nns_t h) {
                       &h->part_keys, &h->res_dev, &h->all_sims, &h->sort_tmp, &h->sort_kv};
     for (DevBuf* b : bufs) b->free();
     h->res_host.free();
+    h->done_host.free();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     if (h->add_ev) cudaEventDestroy(h->add_ev);
   }
@@ -539,7 +585,11 @@ int64_t cslam_nns_size(cslam_nns_t h) { return h ? h->n : -1; }
 int64_t cslam_nns_capacity(cslam_nns_t h) { return h ? h->capacity : -1; }
 int64_t cslam_nns_dim(cslam_nns_t h) { return h ? h->dim : -1; }
 int64_t cslam_nns_ld(cslam_nns_t h) { return h ? h->ld : -1; }
-void* cslam_nns_data_ptr(cslam_nns_t h) { return h ? h->arena.base() : nullptr; }
+void* cslam_nns_data_ptr(cslam_nns_t h) {
+  if (!h) return nullptr;
+  h->data_exposed = true;  // rows may now change without the library knowing: searches are no longer chained
+  return h->arena.base();
+}
 int cslam_nns_device(cslam_nns_t h) { return h ? h->device : -1; }
 
 int cslam_nns_add(cslam_nns_t h, const float* rows, int64_t count, int64_t src_ld, int src_is_device,
@@ -552,6 +602,7 @@ int cslam_nns_add(cslam_nns_t h, const float* rows, int64_t count, int64_t src_l
   cudaStream_t stream = (cudaStream_t)stream_;
   DeviceGuard g(h->device);
   if (count > 0) {
+    h->k1_chain = false;  // the copy is an ordinary stream operation: the next search starts after it
     if (h->n + count > 0xffffffffll) return fail(h, CSLAM_NNS_EINVAL, "more than 2^32 rows");
     int rc = grow_to(h, h->n + count, stream);
     if (rc) return rc;
@@ -636,9 +687,15 @@ int cslam_nns_search(cslam_nns_t h, const float* queries, int64_t B, int64_t q_l
   if (!h->res_host.ensure((size_t)B * k_run * 12)) return fail(h, CSLAM_NNS_ENOMEM, "pinned result buffer");
   long long* hi = (long long*)h->res_host.p;
   float* hs = (float*)(hi + B * k_run);
+  // one query, fused select: the kernel's last CTA publishes a sequence number behind the results and the host
+  // spins on it (mapped pinned memory) instead of synchronising the stream
+  const unsigned seq0 = h->done_seq;
+  h->want_done = B == 1 && k_run <= 32 && h->done_host.ensure(64);
   rc = search_device(h, dq, B, dq_ld, k_run, nullptr, hi, hs, 1, 0, stream);
+  h->want_done = false;
   if (rc) return rc;
-  CK(h, cudaStreamSynchronize(stream));
+  if (h->done_seq != seq0) CK(h, wait_done(h, h->done_seq, stream));
+  else CK(h, cudaStreamSynchronize(stream));
   for (long long b = 0; b < B; ++b) {
     if (out_idx) {
       memcpy(out_idx + b * k, hi + b * k_run, (size_t)k_run * 8);
@@ -773,6 +830,7 @@ int cslam_nns_search_filtered(cslam_nns_t h, const float* queries, int64_t B, in
   long long* hi = (long long*)h->res_host.p;
   float* hsim = (float*)(hi + B * k);
   int* hpos = (int*)(hsim + B * k);
+  h->k1_chain = false;  // the filter kernel sits between this search and the next one
   filter_kernel<<<(unsigned)((B + 127) / 128), 128, 0, stream>>>(
       di, ds, B, k_run, k, (const long long*)h->ids_arena.base(), dqids,
       need_ids ? (long long)query_ids[0] : 0ll, need_ids ? 1 : 0, mode, (long long)min_gap, threshold,

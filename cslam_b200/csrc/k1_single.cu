@@ -64,6 +64,9 @@ struct K1Dev {
   float* out_sim;
   long long idx_stride, idx_offset;
   float* all_sims;
+  int dep_wait;            // execute griddepcontrol.wait once the ring is primed (chained searches, see k1_kernel)
+  unsigned* done_flag;     // mapped host word (or null): receives done_value after the results are written
+  unsigned done_value;
   long long keep_rows;  // rows below this are loaded with L2 evict-last, the rest evict-first (0: no hints)
   long long tiles_div, tiles_rem;  // total tiles / and % (grid * warps): a warp's tile count without a device division
 };
@@ -165,6 +168,13 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     }
   }
   K1_STAMP(tid == 0, 4);  // ring primed (mbarrier init + first S bulk copies issued)
+  // Chained searches of the SAME database (programmatic dependent launch): this grid's CTAs were scheduled as
+  // the previous search's CTAs left their SMs, and the first row tiles are already on their way — rows that
+  // only change through the library's own stream-ordered appends at the END of the database.  Everything else
+  // (the query, the ticket / scratch slot, the output) waits here until the previous grid has completed and
+  // flushed: what overlaps is the launch latency, the prologue and the first-byte latency, not the streams.
+  // A no-op for an ordinary launch.
+  if (p.dep_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
 #ifdef K1_PROF
   if (tid == 1 && my_items > 2) {  // a plain load from a part of the database nobody has touched yet
     const float4* far = p.db + ((gw + 2 * GW) * p.rows_per_tile) * p.ld4 + 8;
@@ -345,6 +355,10 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
         if (p.out_idx) p.out_idx[0] = have ? grow : -1ll;
         if (p.out_sim) p.out_sim[0] = have ? key_sim(key) : -INFINITY;
         *p.ticket = 0u;
+        if (p.done_flag) {  // host destination: the caller spins on this word instead of a stream synchronisation
+          __threadfence_system();
+          *reinterpret_cast<volatile unsigned*>(p.done_flag) = p.done_value;
+        }
       }
     }
     return;
@@ -408,6 +422,11 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
         if (p.out_sim) p.out_sim[lane] = have ? key_sim(key) : -INFINITY;
       }
       if (lane == 0) *p.ticket = 0u;
+      if (p.done_flag) {
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) *reinterpret_cast<volatile unsigned*>(p.done_flag) = p.done_value;
+      }
     }
     return;
   }
@@ -522,6 +541,9 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   p.idx_stride = a.idx_stride;
   p.idx_offset = a.idx_offset;
   p.all_sims = a.all_sims;
+  p.dep_wait = (a.overlap_prev && a.dep_wait) ? 1 : 0;
+  p.done_flag = a.k <= 32 ? a.done_flag : nullptr;
+  p.done_value = a.done_value;
   // Opt-in (off by default, not used for any reported number): keep the first CSLAM_NNS_L2_KEEP_MB of the
   // database resident in L2 across back-to-back searches of the same database.  B200, 100k x 512 (205 MB):
   // 5.58 -> 6.36 TB/s effective at 80 MB, 6.63 at 96 MB, thrashing back to 5.66 at 112 MB.
@@ -603,7 +625,12 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
-  if (a.overlap_prev) {  // see the top of k1_kernel
+  // A chained search of the same database needs every SM to hold exactly one CTA of the previous search (then at
+  // most two searches are ever in flight and the ticket / scratch ring of 4 cannot wrap) and a scan long enough
+  // that the tiles fetched before griddepcontrol.wait are nowhere near the appended tail of the database.
+  const bool chain_ok = !a.dep_wait || (grid == num_sms && p.tiles_div >= 4 * (long long)p.stages);
+  if (!chain_ok) p.dep_wait = 0;
+  if (a.overlap_prev && chain_ok) {  // see the top of k1_kernel
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;

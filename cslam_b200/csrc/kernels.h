@@ -35,7 +35,15 @@ struct K1Args {
   // launch in the stream has vacated.  Only valid when the previous launch is a K1 search that shares no
   // scratch, ticket or output with this one (another database, cslam_nns_search_multi).
   bool overlap_prev = false;
+  // with overlap_prev: the previous launch searched the SAME database (same handle): the kernel then waits for
+  // it (griddepcontrol.wait) right after priming its ring, before it touches the query, its ticket / scratch
+  // slot or the output.  false = independent databases (cslam_nns_search_multi): no wait at all.
+  bool dep_wait = false;
+  // host destination: mapped pinned word that receives done_value once the results are written (k <= 32 only)
+  unsigned* done_flag = nullptr;
+  unsigned done_value = 0;
 };
+static constexpr int kK1Slots = 4;  // ring of ticket / scratch sets used by chained searches of one database
 
 // Maximum grid K1 will ever use on `device` (sizes the scratch buffer).
 int k1_max_grid(int num_sms);
