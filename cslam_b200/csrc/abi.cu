@@ -389,8 +389,8 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
     // are none, so the call stays stream-ordered without a host round trip.
     if (screen) {
       if (!h->screen_stats.p) {
-        if (!h->screen_stats.ensure(16)) return fail(h, CSLAM_NNS_ENOMEM, "screening counters");
-        CK(h, cudaMemsetAsync(h->screen_stats.p, 0, 16, stream));
+        if (!h->screen_stats.ensure(64)) return fail(h, CSLAM_NNS_ENOMEM, "screening counters");
+        CK(h, cudaMemsetAsync(h->screen_stats.p, 0, 64, stream));
       }
       a.screen = true;
       a.k = kl;
@@ -419,9 +419,11 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       r.idx_stride = idx_stride;
       r.idx_offset = idx_offset;
       r.stats = (unsigned long long*)h->screen_stats.p;
+      if (env_int("CSLAM_NNS_K6_TRACE", 0) && h->sort_kv.ensure((size_t)Bc * 64 * 8)) r.debug = (u64*)h->sort_kv.p;
       CK(h, k6_rescore(r, stream));
       DBG_SYNC(h, stream, "after k6_rescore");
       const unsigned* tail = (const unsigned*)h->inv_qn.p + (size_t)kQParPlanes * Bc;
+      if (env_int("CSLAM_NNS_SCREEN_NOFB", 0)) continue;   // development: leave the screening pass's lists in place
       a.screen = false;
       a.k = k_run;
       a.active_mask = tail;
@@ -954,6 +956,16 @@ int cslam_nns_set_variant(cslam_nns_t h, int variant) {
 }
 int cslam_nns_last_variant(cslam_nns_t h) { return h ? h->last_variant : -1; }
 
+// development: copy an internal device buffer to the host (0 = partial key lists, 1 = query parameter block)
+int cslam_nns_debug_copy(cslam_nns_t h, int what, void* dst, int64_t bytes) {
+  if (!h || !dst || bytes <= 0) return CSLAM_NNS_EINVAL;
+  DeviceGuard g(h->device);
+  const DevBuf& b = what == 0 ? h->part_keys : what == 2 ? h->sort_kv : h->inv_qn;
+  if (!b.p || (size_t)bytes > b.bytes) return fail(h, CSLAM_NNS_EINVAL, "debug buffer smaller than requested");
+  CK(h, cudaMemcpy(dst, b.p, (size_t)bytes, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 int cslam_nns_set_screen(cslam_nns_t h, int enable, int64_t min_rows) {
   if (!h) return CSLAM_NNS_EINVAL;
   h->screen = enable != 0;
@@ -963,13 +975,17 @@ int cslam_nns_set_screen(cslam_nns_t h, int enable, int64_t min_rows) {
 
 int cslam_nns_screen_stats(cslam_nns_t h, int64_t* screened, int64_t* fallback) {
   if (!h) return CSLAM_NNS_EINVAL;
-  unsigned long long v[2] = {0ull, 0ull};
+  unsigned long long v[8] = {};
   if (h->screen_stats.p) {
     DeviceGuard g(h->device);
     CK(h, cudaMemcpy(v, h->screen_stats.p, sizeof v, cudaMemcpyDeviceToHost));
   }
   if (screened) *screened = (int64_t)v[0];
   if (fallback) *fallback = (int64_t)v[1];
+  if (env_int("CSLAM_NNS_SCREEN_VERBOSE", 0))
+    fprintf(stderr, "[screen] screened %llu fallback %llu: nan/bad %llu, < k candidates %llu, band overflow %llu, "
+                    "outside bound too close %llu, nan bound %llu, bad rows %llu\n", v[0], v[1], v[2], v[3], v[4], v[5],
+            v[6], v[7]);
   return 0;
 }
 

@@ -19,14 +19,15 @@
 //      from a list, against a full list's smallest entry or against the shared bound, and the shared bound at the
 //      end of the pass is >= every full list's smallest entry (offer_key publishes it whenever it grows).
 //
-// Per query (one CTA): take the k best candidates by s~ out of the union of the lists, re-score them exactly:
-// their smallest exact similarity L0 is a lower bound of the final k-th best.  Re-score every other candidate
-// with s~ >= L0 - E_q (the "band": by (1) nothing else in the union can reach L0).  If tau_q < L0 - E_q, by (1)
-// and (2) no row outside the union can reach L0 either, so the k best exact keys among the re-scored rows ARE
-// the exact top-k of the whole database: they are written out (sorted, lower row first on equal similarity,
-// like every other path).  Otherwise — tau_q too close (databases full of near-duplicates), more than kBandCap
-// rows in the band, NaN anywhere — the query's bit is set in the fallback mask and the masked 3xTF32 pass
-// queued right behind this kernel recomputes it; that pass exits at once when no bit is set.
+// Per query (one CTA): T = the k-th largest screened similarity in the union of the lists (radix select over the
+// ordered-uint keys in shared memory).  The k candidates at or above T have exact similarities >= T - E_q by (1),
+// so L = T - E_q is a lower bound of the final k-th best, and by (1) again no row with s~ < lim = T - 2 E_q can
+// reach L.  Every candidate of the union with s~ >= lim (the "band") is re-scored exactly.  If tau_q < lim, by (2)
+// no row outside the union can reach L either, so the k best exact keys among the re-scored rows ARE the exact
+// top-k of the whole database: they are written out (sorted, lower row first on equal similarity, like every
+// other path).  Otherwise — tau_q too close (databases full of near-duplicates), more than kBandCap rows in the
+// band, NaN anywhere — the query's bit is set in the fallback mask and the masked 3xTF32 pass queued right behind
+// this kernel recomputes it; that pass exits at once when no bit is set.
 //
 // Latency-bound: B * (k + band) rows of ld * 4 bytes (C3: 256 x ~40 x 16 KB = 170 MB, ~1 % of the pass).
 #include "common.cuh"
@@ -36,8 +37,7 @@ namespace cslam {
 namespace {
 
 constexpr int W6 = 8;            // warps per CTA
-constexpr int kBandCap = 224;    // rows beyond the screened top-k one query may re-score before giving up
-constexpr int kMaxExact = 32 + kBandCap;
+constexpr int kBandCap = 256;    // candidates one query may re-score before giving up
 
 struct K6Dev {
   const float* db;
@@ -58,6 +58,7 @@ struct K6Dev {
   unsigned* fail_count;
   unsigned long long* stats;
   int kl;  // capacity of the screening pass's lists (>= k)
+  u64* debug;  // development: 64 words per query (top-k keys by s~, counters), or null
 };
 
 __device__ __forceinline__ void fma4x(const float4& x, const float4& q, float& dot, float& nn) {
@@ -107,13 +108,12 @@ __device__ __forceinline__ float warp_exact_sim(const float* __restrict__ row, c
 
 __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   extern __shared__ __align__(16) unsigned char smem6[];
-  u64* keys = reinterpret_cast<u64*>(smem6);  // the union of this query's lists: [parts * k]
-  __shared__ u64 wl[W6 * 32];                 // per-warp top-k by s~
-  __shared__ u64 topk[32];                    // the k best candidates by s~, descending
-  __shared__ u64 exact[kMaxExact];            // exact keys of everything re-scored
-  __shared__ u64 band[kBandCap];
+  u64* keys = reinterpret_cast<u64*>(smem6);  // the union of this query's lists: [parts * kl]
+  __shared__ u64 band[kBandCap];              // candidates to re-score
+  __shared__ u64 exact[kBandCap];             // their exact keys
   __shared__ u64 outk[32];
-  __shared__ float exs[32];
+  __shared__ unsigned hist[256];
+  __shared__ unsigned sel_prefix, sel_want, n_keys;
   __shared__ int band_cnt, bad;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x, k = p.k, kl = p.kl;
@@ -121,105 +121,133 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   if (tid == 0) {
     band_cnt = 0;
     bad = 0;
+    n_keys = 0u;
+    sel_prefix = 0u;
+    sel_want = (unsigned)k;
     if (b == 0 && p.stats) atomicAdd(p.stats, (unsigned long long)p.B);
   }
-  if (tid < 32) {
-    outk[tid] = 0ull;
-    exs[tid] = 0.f;
-  }
+  if (tid < 32) outk[tid] = 0ull;
   __syncthreads();
 
-  // ---- 1. the union of the lists -> shared memory; its k best keys by s~ -------------------------------------
-  u64 thr = 0ull, mine = 0ull;
-  int saw_nan = 0;
-  for (int base = 0; base < total; base += W6 * 32) {
-    const int i = base + tid;
-    u64 key = 0ull;
-    if (i < total) {
+  // ---- 1. the union of the lists -> shared memory ------------------------------------------------------------------
+  {
+    unsigned mine_n = 0u;
+    int saw_nan = 0;
+    for (int i = tid; i < total; i += W6 * 32) {
       const int part = i / kl, j = i - part * kl;
-      key = __ldcg(p.part_keys + ((size_t)part * p.B + b) * kl + j);
+      const u64 key = __ldcg(p.part_keys + ((size_t)part * p.B + b) * kl + j);
       keys[i] = key;
+      mine_n += key != 0ull;
       saw_nan |= ((unsigned)(key >> 32) == 0xffffffffu);
     }
-    offer(nullptr, k, key, key != 0ull, thr, mine, lane);
-  }
-  if (k == 1) mine = lane == 0 ? thr : 0ull;  // offer() keeps the k == 1 winner in `thr`
-  wl[warp * 32 + lane] = lane < k ? mine : 0ull;
-  if (saw_nan) bad = 1;  // NaN similarities sort first in the reference: left to the 3xTF32 pass
-  __syncthreads();
-  if (warp == 0) {
-    u64 v = wl[lane];
-#pragma unroll
-    for (int w = 1; w < W6; ++w) v = warp_merge_desc(v, wl[w * 32 + lane], lane);
-    topk[lane] = lane < k ? v : 0ull;
+    if (mine_n) atomicAdd(&n_keys, mine_n);
+    if (saw_nan) bad = 1;  // NaN similarities sort first in the reference: left to the 3xTF32 pass
   }
   __syncthreads();
-  int m_top = 0;
-  for (int j = 0; j < k; ++j) m_top += topk[j] != 0ull;
-  const float* q = p.q + (size_t)b * p.q_ld;
-  const float inv_qn = p.inv_qn[b];
+  const bool enough = n_keys >= (unsigned)k;
 
-  // ---- 2. exact similarities of those k rows: the smallest one, L0, bounds the final k-th best from below ------
-  for (int j = warp; j < m_top; j += W6) {
-    const uint32_t row = key_row(topk[j]);
-    if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
-      if (lane == 0) { exact[j] = 0ull; exs[j] = 0.f; bad = 1; }
-      continue;
-    }
-    const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
-    if (lane == 0) {
-      exact[j] = make_key(s, row);
-      exs[j] = s;
+  // ---- 2. T = the k-th largest screened similarity of the union (as an ordered uint): radix select, 8 bits per
+  //         pass, most significant first (a shared-memory histogram; thread 0 walks the 256 bins) ----------------------
+  if (enough) {
+    for (int pass = 0; pass < 4; ++pass) {
+      const int shift = 24 - 8 * pass;
+      hist[tid] = 0u;   // W6 * 32 == 256 threads
+      __syncthreads();
+      const unsigned prefix = sel_prefix;
+      for (int i = tid; i < total; i += W6 * 32) {
+        const u64 key = keys[i];
+        if (key == 0ull) continue;
+        const unsigned ord = (unsigned)(key >> 32);
+        if (pass == 0 || (ord >> (shift + 8)) == prefix) atomicAdd(&hist[(ord >> shift) & 255u], 1u);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        unsigned want = sel_want, acc = 0u;
+        int bin = 255;
+        for (; bin > 0; --bin) {
+          if (acc + hist[bin] >= want) break;
+          acc += hist[bin];
+        }
+        sel_want = want - acc;              // rank of the k-th largest inside the chosen bin
+        sel_prefix = (prefix << 8) | (unsigned)bin;
+      }
+      __syncthreads();
     }
   }
-  __syncthreads();
-  float l0 = INFINITY;
-  for (int j = 0; j < m_top; ++j) l0 = fminf(l0, exs[j]);  // fminf skips NaN: checked separately below
-  bool nan_exact = false;
-  for (int j = 0; j < m_top; ++j) nan_exact |= !(exs[j] == exs[j]);
+  // Every one of the k candidates with ord >= T has an exact similarity >= sim(T) - E, so the final k-th best is
+  // >= sim(T) - E, and no row whose screened similarity is below lim = sim(T) - 2E can reach it.
   const float E = p.ebound[b];
-  const float lim = l0 - E;
-  const u64 kth = m_top > 0 ? topk[m_top - 1] : 0ull;
+  const float lim = ord_to_sim(sel_prefix) - 2.0f * E;
 
-  // ---- 3. the band: every other candidate whose screened similarity could still reach L0 -------------------------
-  for (int i = tid; i < total; i += W6 * 32) {
-    const u64 key = keys[i];
-    if (key != 0ull && key < kth && key_sim(key) >= lim) {
-      const int at = atomicAdd(&band_cnt, 1);
-      if (at < kBandCap) band[at] = key;
+  // ---- 3. the band: every candidate of the union whose screened similarity is >= lim ------------------------------
+  if (enough && lim == lim) {
+    for (int i = tid; i < total; i += W6 * 32) {
+      const u64 key = keys[i];
+      if (key != 0ull && key_sim(key) >= lim) {
+        const int at = atomicAdd(&band_cnt, 1);
+        if (at < kBandCap) band[at] = key;
+      }
     }
   }
   __syncthreads();
   const int nband = band_cnt;
   const int m = nband < kBandCap ? nband : kBandCap;
+
+  // ---- 4. exact fp32 similarities of the band (one row per warp at a time) ------------------------------------------
+  const float* q = p.q + (size_t)b * p.q_ld;
+  const float inv_qn = p.inv_qn[b];
   for (int j = warp; j < m; j += W6) {
     const uint32_t row = key_row(band[j]);
-    if ((long long)row >= p.n) {
-      if (lane == 0) { exact[m_top + j] = 0ull; bad = 1; }
+    if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
+      if (lane == 0) {
+        exact[j] = 0ull;
+        bad = 1;
+        if (p.stats) atomicAdd(p.stats + 7, 1ull);
+      }
       continue;
     }
     const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
     if (lane == 0) {
-      exact[m_top + j] = make_key(s, row);
+      exact[j] = make_key(s, row);
       if (!(s == s)) bad = 1;
     }
   }
   __syncthreads();
 
-  // ---- 4. the proof, or the fallback -------------------------------------------------------------------------------
+  // ---- 5. the proof, or the fallback -------------------------------------------------------------------------------
   const unsigned g = __ldcg(p.gthr + b);
   // g == 0: no list ever filled up, nothing was dropped anywhere: the union is the whole database
   const bool outside_ok = g == 0u || (ord_to_sim(g) < lim);
-  const bool proven = !bad && !nan_exact && m_top == k && nband <= kBandCap && outside_ok && (lim == lim);
+  const bool proven = !bad && enough && nband >= k && nband <= kBandCap && outside_ok && (lim == lim);
+  if (p.debug && tid == 0) {
+    u64* d = p.debug + (size_t)b * 64;
+    for (int j = 0; j < 24; ++j) d[j] = j < m ? band[j] : 0ull;
+    for (int j = 0; j < 24; ++j) d[24 + j] = j < m ? exact[j] : 0ull;
+    d[48] = (u64)n_keys;
+    d[49] = (u64)nband;
+    d[50] = (u64)sel_prefix;
+    d[51] = (u64)__float_as_uint(lim);
+    d[52] = (u64)g;
+    d[53] = (u64)__float_as_uint(E);
+    d[54] = (u64)bad;
+    d[55] = (u64)p.n;
+    d[56] = (u64)total;
+  }
   if (!proven) {
     if (tid == 0) {
       atomicOr(p.fail_mask + (b >> 5), 1u << (b & 31));
       atomicAdd(p.fail_count, 1u);
-      if (p.stats) atomicAdd(p.stats + 1, 1ull);
+      if (p.stats) {
+        atomicAdd(p.stats + 1, 1ull);
+        // why (first reason that applies): 2 NaN / bad row, 3 fewer than k candidates, 4 band overflow,
+        // 5 the bound of the rows outside the lists is too close, 6 NaN bound
+        const int why = bad ? 2 : (!enough || nband < k) ? 3 : nband > kBandCap ? 4 : !outside_ok ? 5 : 6;
+        atomicAdd(p.stats + why, 1ull);
+      }
     }
     return;
   }
-  block_rank_select(exact, m_top + m, k, outk);
+  block_rank_select(exact, m, k, outk);
   __syncthreads();
   if (tid < k) {
     const u64 key = outk[tid];
@@ -260,6 +288,7 @@ cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
   p.fail_count = tail + 8;
   p.stats = a.stats;
   p.kl = a.kl;
+  p.debug = a.debug;
   const size_t smem = (size_t)a.parts * a.kl * 8;
   if (smem > 40 * 1024) return cudaErrorInvalidConfiguration;
   k6_kernel<<<(unsigned)a.B, W6 * 32, smem, stream>>>(p);

@@ -84,6 +84,7 @@ struct K6Args {
   float* out_sim;
   long long idx_stride, idx_offset;
   unsigned long long* stats;  // [0] += queries screened, [1] += queries handed to the fallback
+  u64* debug = nullptr;       // development: 64 words per query
 };
 cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream);
 // the per-query shared threshold plane the query-major batched kernel leaves behind ([B] ordered uints inside

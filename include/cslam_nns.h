@@ -212,6 +212,9 @@ int cslam_nns_set_screen(cslam_nns_t h, int enable, int64_t min_rows);
 /* Counters since the handle was created: queries that went through the screening pass, and how many of them the
  * proof did not cover (recomputed by the 3xTF32 pass).  Synchronises the device. */
 int cslam_nns_screen_stats(cslam_nns_t h, int64_t* screened, int64_t* fallback);
+/* Development aid: copy an internal device buffer of the last batched search to the host (what = 0: the partial
+ * key lists, 1: the per-query parameter block).  Synchronises the device. */
+int cslam_nns_debug_copy(cslam_nns_t h, int what, void* dst, int64_t bytes);
 /* Time in milliseconds (CUDA events on `stream`) of `iters` back-to-back device-resident searches of
  * the same query block: the kernel-only figure the roofline is computed from.  queries_dev is device
  * memory; results are discarded.  Returns the per-search average in *ms_per_search. */

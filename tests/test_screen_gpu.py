@@ -73,7 +73,7 @@ def test_neighbours_in_consecutive_rows_are_proven_without_fallback():
     eps = synth.normal(85, (B, 9, d)).astype(np.float32)
     for j in range(B):                       # query j revisits a place seen at rows 200 j + 100 .. + 108
         for t in range(9):
-            v = qs[j] + (0.03 + 0.01 * t) * eps[j, t]
+            v = qs[j] + (0.010 + 0.003 * t) * eps[j, t]
             db[200 * j + 100 + t] = v / np.linalg.norm(v)
     m = _matcher(db)
     idx, sims = m._search_block(torch.from_numpy(qs), k)
