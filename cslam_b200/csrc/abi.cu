@@ -692,7 +692,9 @@ int cslam_nns_search(cslam_nns_t h, const float* queries, int64_t B, int64_t q_l
   // one query, fused select: the kernel's last CTA publishes a sequence number behind the results and the host
   // spins on it (mapped pinned memory) instead of synchronising the stream
   const unsigned seq0 = h->done_seq;
-  h->want_done = B == 1 && k_run <= 32 && h->done_host.ensure(64);
+  if (B == 1 && k_run <= 32 && !h->done_host.p && h->done_host.ensure(64))
+    memset(h->done_host.p, 0, 64);   // a recycled pinned block may still hold another handle's last sequence number
+  h->want_done = B == 1 && k_run <= 32 && h->done_host.p != nullptr;
   rc = search_device(h, dq, B, dq_ld, k_run, nullptr, hi, hs, 1, 0, stream);
   h->want_done = false;
   if (rc) return rc;

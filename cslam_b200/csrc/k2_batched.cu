@@ -452,16 +452,19 @@ __global__ void k2_prepare_kernel(const float* __restrict__ q, int dim, int q_ld
     // yet) of the first pass (the only one, or the screening pass) and of the masked fallback pass
     reinterpret_cast<unsigned*>(inv_qn + kQParGthr * B)[b] = 0u;
     reinterpret_cast<unsigned*>(inv_qn + kQParGthrFull * B)[b] = 0u;
-    // plane 4: E_q, a bound on |screened similarity - exact fp32 similarity| for ANY row (k6_rescore.cu has
-    // the derivation): operands cut to tf32 (2^-10 relative each: 2^-9 of sum |x_i||q_i - c| <= |x||q - c|),
-    // fp32 accumulation in tensor memory (dim / 8 instructions, bounded generously by dim ulps), the fp32 sums
-    // |x|^2 and sum(x) of the converter (dim / 4 sequential adds), epilogue and re-scoring roundings; x 1.25
+    // plane 4: E_q, a bound on |screened similarity - exact fp32 similarity| for ANY row (k6_rescore.cu has the
+    // derivation).  Operands: the tensor core cuts x to tf32 (relative error < 2^-10), q - c was rounded to
+    // tf32 above (<= 2^-11): together (2^-10 + 2^-11 + 2^-21) * sum |x_i| |q_i - c| <= 1.5 * 2^-10 |x| |q - c|.
+    // Accumulation in tensor memory: dim / 8 instructions, each at most one fp32 ulp of the running sum for the
+    // add and one for aligning its 8 products: dim / 4 ulps of at most |x| |q - c|.  The converter's fp32
+    // |x|^2 and sum(x) (dim / 4 sequential adds each, the latter scaled by c), the epilogue's and the
+    // re-scoring's roundings: the last two terms.  x 1.125 on top.
     const float dev2 = fmaxf(t - (float)dim * mean_s * mean_s, 0.f);      // |q - c|^2
     const float rho = sqrtf(dev2) * invq;
     const float fd = (float)dim;
-    const float e = (1.953125e-3f + fd * 1.1920929e-7f) * rho +
+    const float e = (1.4653e-3f + (0.25f * fd + 16.f) * 1.1920929e-7f) * rho +
                     (0.25f * fd + 8.f) * 5.9604645e-8f * (1.f + fabsf(mean_s) * sqrtf(fd) * invq) + 2e-6f;
-    inv_qn[kQParEbound * B + b] = 1.25f * e;      // NaN for a NaN query: every comparison fails -> fallback
+    inv_qn[kQParEbound * B + b] = 1.125f * e;      // NaN for a NaN query: every comparison fails -> fallback
     if (b == 0) {
       unsigned* w = reinterpret_cast<unsigned*>(inv_qn + kQParPlanes * B);
       for (int i = 0; i < kQParTailWords; ++i) w[i] = 0u;   // fail mask [0..7], fail count [8]
@@ -471,7 +474,9 @@ __global__ void k2_prepare_kernel(const float* __restrict__ q, int dim, int q_ld
   const float c = mean_s;
   for (int i = threadIdx.x; i < q_ld; i += blockDim.x) {
     const float x = i < dim ? src[i] - c : 0.f;
-    const float h = tf32_hi(x);
+    // round to nearest: |q - c - h| <= 2^-11 |q - c| (a cut would be 2^-10), which the screening pass's error
+    // bound relies on; h is tf32-exact either way and the residual below completes it for the 3xTF32 pass
+    const float h = tf32_rna(x);
     q_hi[(size_t)b * q_ld + i] = h;
     q_lo[(size_t)b * q_ld + i] = tf32_rna(x - h);
   }

@@ -11,20 +11,21 @@
 //
 //  (1) |s~(x) - s(x)| <= E_q for EVERY row x, s being the fp32 similarity this kernel computes.  The operands are
 //      cut to tf32 (relative error < 2^-10 each), so the dot product is off by at most
-//      (2^-9 + 2^-20) * sum_i |x_i| |q_i - c| <= 2^-9 |x| |q - c| (Cauchy-Schwarz); dividing by |x| |q| leaves
-//      2^-9 * rho_q, rho_q = |q - c| / |q| — independent of the row.  The remaining terms (fp32 accumulation in
+//      1.5 * 2^-10 * sum_i |x_i| |q_i - c| <= 1.5 * 2^-10 |x| |q - c| (x is cut to tf32 by the tensor core, q - c
+//      was rounded to tf32 by k2_prepare; Cauchy-Schwarz); dividing by |x| |q| leaves 1.5 * 2^-10 * rho_q,
+//      rho_q = |q - c| / |q| — independent of the row.  The remaining terms (fp32 accumulation in
 //      tensor memory, the converter's fp32 |x|^2 and sum(x), epilogue and re-scoring roundings) are bounded in
-//      k2_prepare, which writes E_q (x 1.25) next to the other per-query parameters.
+//      k2_prepare, which writes E_q (x 1.125) next to the other per-query parameters.
 //  (2) Every row that is in NONE of the query's lists has s~ <= tau_q: a row is only ever dropped, or evicted
 //      from a list, against a full list's smallest entry or against the shared bound, and the shared bound at the
 //      end of the pass is >= every full list's smallest entry (offer_key publishes it whenever it grows).
 //
 // Per query (one CTA): T = the k-th largest screened similarity in the union of the lists (radix select over the
-// ordered-uint keys in shared memory).  The k candidates at or above T have exact similarities >= T - E_q by (1),
-// so L = T - E_q is a lower bound of the final k-th best, and by (1) again no row with s~ < lim = T - 2 E_q can
-// reach L.  Every candidate of the union with s~ >= lim (the "band") is re-scored exactly.  If tau_q < lim, by (2)
-// no row outside the union can reach L either, so the k best exact keys among the re-scored rows ARE the exact
-// top-k of the whole database: they are written out (sorted, lower row first on equal similarity, like every
+// ordered-uint keys in shared memory).  The (>= k) candidates at or above T are re-scored exactly; the k-th largest
+// of their exact similarities, L0, is a lower bound of the final k-th best, and by (1) no row with s~ < lim =
+// L0 - E_q can reach it.  Every other candidate of the union with s~ >= lim (the "band") is re-scored as well.  If
+// tau_q < lim, by (2) no row outside the union can reach L0 either, so the k best exact keys among the re-scored
+// rows ARE the exact top-k of the whole database: they are written out (sorted, lower row first on equal similarity, like every
 // other path).  Otherwise — tau_q too close (databases full of near-duplicates), more than kBandCap rows in the
 // band, NaN anywhere — the query's bit is set in the fallback mask and the masked 3xTF32 pass queued right behind
 // this kernel recomputes it; that pass exits at once when no bit is set.
@@ -37,7 +38,7 @@ namespace cslam {
 namespace {
 
 constexpr int W6 = 8;            // warps per CTA
-constexpr int kBandCap = 256;    // candidates one query may re-score before giving up
+constexpr int kBandCap = 384;    // candidates one query may re-score before giving up
 
 struct K6Dev {
   const float* db;
@@ -174,44 +175,69 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
       __syncthreads();
     }
   }
-  // Every one of the k candidates with ord >= T has an exact similarity >= sim(T) - E, so the final k-th best is
-  // >= sim(T) - E, and no row whose screened similarity is below lim = sim(T) - 2E can reach it.
   const float E = p.ebound[b];
-  const float lim = ord_to_sim(sel_prefix) - 2.0f * E;
+  const unsigned T = sel_prefix;
+  const float* q = p.q + (size_t)b * p.q_ld;
+  const float inv_qn = p.inv_qn[b];
 
-  // ---- 3. the band: every candidate of the union whose screened similarity is >= lim ------------------------------
-  if (enough && lim == lim) {
+  // re-score band[from, to) into exact[from, to): one row per warp at a time
+  auto rescore = [&](int from, int to) {
+    for (int j = from + warp; j < to; j += W6) {
+      const uint32_t row = key_row(band[j]);
+      if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
+        if (lane == 0) {
+          exact[j] = 0ull;
+          bad = 1;
+          if (p.stats) atomicAdd(p.stats + 7, 1ull);
+        }
+        continue;
+      }
+      const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
+      if (lane == 0) {
+        exact[j] = make_key(s, row);
+        if (!(s == s)) bad = 1;
+      }
+    }
+  };
+
+  // ---- 3. the (>= k) candidates at or above T, re-scored: the k-th largest of their exact similarities, L0, is a
+  //         lower bound of the final k-th best ------------------------------------------------------------------------
+  if (enough) {
     for (int i = tid; i < total; i += W6 * 32) {
       const u64 key = keys[i];
-      if (key != 0ull && key_sim(key) >= lim) {
+      if (key != 0ull && (unsigned)(key >> 32) >= T) {
         const int at = atomicAdd(&band_cnt, 1);
         if (at < kBandCap) band[at] = key;
       }
     }
   }
   __syncthreads();
-  const int nband = band_cnt;
-  const int m = nband < kBandCap ? nband : kBandCap;
+  const int ntop = band_cnt < kBandCap ? band_cnt : kBandCap;   // > k only through ties at T
+  rescore(0, ntop);
+  __syncthreads();
+  if (tid < 32) outk[tid] = 0ull;
+  __syncthreads();
+  block_rank_select(exact, ntop, k, outk);   // outk[k - 1] = the k-th largest exact key so far
+  __syncthreads();
+  const float l0 = ntop >= k ? key_sim(outk[k - 1]) : __int_as_float(0x7fc00000);
+  const float lim = l0 - E;   // by (1) no row whose screened similarity is below lim can reach l0
+  __syncthreads();            // everybody has read outk before it is cleared again below
 
-  // ---- 4. exact fp32 similarities of the band (one row per warp at a time) ------------------------------------------
-  const float* q = p.q + (size_t)b * p.q_ld;
-  const float inv_qn = p.inv_qn[b];
-  for (int j = warp; j < m; j += W6) {
-    const uint32_t row = key_row(band[j]);
-    if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
-      if (lane == 0) {
-        exact[j] = 0ull;
-        bad = 1;
-        if (p.stats) atomicAdd(p.stats + 7, 1ull);
+  // ---- 4. the band: every OTHER candidate of the union whose screened similarity is >= lim, re-scored too --------
+  if (enough && lim == lim && band_cnt <= kBandCap) {
+    for (int i = tid; i < total; i += W6 * 32) {
+      const u64 key = keys[i];
+      if (key != 0ull && (unsigned)(key >> 32) < T && key_sim(key) >= lim) {
+        const int at = atomicAdd(&band_cnt, 1);
+        if (at < kBandCap) band[at] = key;
       }
-      continue;
-    }
-    const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
-    if (lane == 0) {
-      exact[j] = make_key(s, row);
-      if (!(s == s)) bad = 1;
     }
   }
+  if (tid < 32) outk[tid] = 0ull;
+  __syncthreads();
+  const int nband = band_cnt;
+  const int m = nband < kBandCap ? nband : kBandCap;
+  rescore(ntop, m);
   __syncthreads();
 
   // ---- 5. the proof, or the fallback -------------------------------------------------------------------------------
@@ -227,6 +253,8 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     d[49] = (u64)nband;
     d[50] = (u64)sel_prefix;
     d[51] = (u64)__float_as_uint(lim);
+    d[57] = (u64)ntop;
+    d[58] = (u64)__float_as_uint(l0);
     d[52] = (u64)g;
     d[53] = (u64)__float_as_uint(E);
     d[54] = (u64)bad;
