@@ -82,6 +82,20 @@ __device__ __forceinline__ float warp_exact_sim(const float* __restrict__ row, c
   const int full4 = dim >> 2;  // float4s that lie entirely inside the descriptor
   float d0 = 0.f, n0 = 0.f, d1 = 0.f, n1 = 0.f, d2 = 0.f, n2 = 0.f, d3 = 0.f, n3 = 0.f;
   int j = lane;
+  // 8 independent 16-byte row loads per lane in flight (4 KB per warp): the rows are scattered over the database,
+  // so this kernel lives on memory-level parallelism; the query comes out of L1
+  for (; j + 224 < full4; j += 256) {
+    float4 x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) x[u] = __ldg(r4 + j + 32 * u);
+#pragma unroll
+    for (int u = 0; u < 8; u += 4) {
+      fma4x(x[u + 0], __ldg(q4 + j + 32 * (u + 0)), d0, n0);
+      fma4x(x[u + 1], __ldg(q4 + j + 32 * (u + 1)), d1, n1);
+      fma4x(x[u + 2], __ldg(q4 + j + 32 * (u + 2)), d2, n2);
+      fma4x(x[u + 3], __ldg(q4 + j + 32 * (u + 3)), d3, n3);
+    }
+  }
   for (; j + 96 < full4; j += 128) {
     const float4 x0 = __ldg(r4 + j), x1 = __ldg(r4 + j + 32), x2 = __ldg(r4 + j + 64), x3 = __ldg(r4 + j + 96);
     const float4 y0 = __ldg(q4 + j), y1 = __ldg(q4 + j + 32), y2 = __ldg(q4 + j + 64), y3 = __ldg(q4 + j + 96);
@@ -155,11 +169,19 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
       hist[tid] = 0u;   // W6 * 32 == 256 threads
       __syncthreads();
       const unsigned prefix = sel_prefix;
-      for (int i = tid; i < total; i += W6 * 32) {
-        const u64 key = keys[i];
-        if (key == 0ull) continue;
-        const unsigned ord = (unsigned)(key >> 32);
-        if (pass == 0 || (ord >> (shift + 8)) == prefix) atomicAdd(&hist[(ord >> shift) & 255u], 1u);
+      // the similarities of a query's candidates share their leading bits, so nearly every key of a pass falls
+      // into the same bin: the lanes of a warp that hit the same bin are counted with ONE shared-memory atomic
+      // (match.any), otherwise the 3 500 same-address atomics of a pass serialise
+      for (int base = 0; base < total; base += W6 * 32) {
+        const int i = base + tid;
+        unsigned bin = 0xffffffffu;
+        if (i < total) {
+          const u64 key = keys[i];
+          const unsigned ord = (unsigned)(key >> 32);
+          if (key != 0ull && (pass == 0 || (ord >> (shift + 8)) == prefix)) bin = (ord >> shift) & 255u;
+        }
+        const unsigned peers = __match_any_sync(kFull, bin);
+        if (bin != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
       }
       __syncthreads();
       if (tid == 0) {
