@@ -184,15 +184,34 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
         if (bin != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
       }
       __syncthreads();
-      if (tid == 0) {
-        unsigned want = sel_want, acc = 0u;
-        int bin = 255;
-        for (; bin > 0; --bin) {
-          if (acc + hist[bin] >= want) break;
-          acc += hist[bin];
+      if (warp == 0) {
+        // walk the 256 bins from the top until `want` keys are covered: lane l owns bins 255 - 8l .. 248 - 8l
+        // (a serial walk by one thread cost ~20 us per query: 1000 dependent shared-memory loads)
+        const unsigned want = sel_want;
+        unsigned c[8], mine = 0u;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          c[u] = hist[255 - 8 * lane - u];
+          mine += c[u];
         }
-        sel_want = want - acc;              // rank of the k-th largest inside the chosen bin
-        sel_prefix = (prefix << 8) | (unsigned)bin;
+        unsigned incl = mine;  // inclusive prefix over lanes 0..lane (bins 255 .. 248 - 8 lane)
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+          const unsigned o = __shfl_up_sync(kFull, incl, off);
+          if (lane >= off) incl += o;
+        }
+        const unsigned hit = __ballot_sync(kFull, incl >= want);   // never empty: `enough` keys exist
+        const int owner = hit ? __ffs(hit) - 1 : 31;
+        if (lane == owner) {
+          unsigned acc = incl - mine;   // keys in the bins above this lane's
+          int u = 0;
+          for (; u < 7; ++u) {
+            if (acc + c[u] >= want) break;
+            acc += c[u];
+          }
+          sel_want = want - acc;                                   // rank of the k-th largest inside the chosen bin
+          sel_prefix = (prefix << 8) | (unsigned)(255 - 8 * lane - u);
+        }
       }
       __syncthreads();
     }
