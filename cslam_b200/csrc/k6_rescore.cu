@@ -73,18 +73,14 @@ __device__ __forceinline__ void fma4x(const float4& x, const float4& q, float& d
   nn = fmaf(x.w, x.w, nn);
 }
 
-// fp32 cosine similarity of one database row with the query, computed by a whole warp; the same formula as
-// the single-query kernel: x.q * rsqrt(max(|x|^2, eps^2)) * (1 / max(|q|, eps))   (nns_matching.py:61)
-__device__ __forceinline__ float warp_exact_sim(const float* __restrict__ row, const float* __restrict__ q,
-                                                int dim, float inv_qn, int lane) {
-  const float4* r4 = reinterpret_cast<const float4*>(row);
-  const float4* q4 = reinterpret_cast<const float4*>(q);
-  const int full4 = dim >> 2;  // float4s that lie entirely inside the descriptor
+// Partial sums x.q and |x|^2 of one database row over the float4 range [a, b), computed by a whole warp (every lane
+// returns the warp's totals).  8 independent 16-byte row loads per lane are in flight (4 KB per warp): the rows are
+// scattered over the database, so this kernel lives on memory-level parallelism; the query comes out of L1.
+__device__ __forceinline__ void warp_partial(const float4* __restrict__ r4, const float4* __restrict__ q4, int a,
+                                             int b, int lane, float& dot_out, float& nn_out) {
   float d0 = 0.f, n0 = 0.f, d1 = 0.f, n1 = 0.f, d2 = 0.f, n2 = 0.f, d3 = 0.f, n3 = 0.f;
-  int j = lane;
-  // 8 independent 16-byte row loads per lane in flight (4 KB per warp): the rows are scattered over the database,
-  // so this kernel lives on memory-level parallelism; the query comes out of L1
-  for (; j + 224 < full4; j += 256) {
+  int j = a + lane;
+  for (; j + 224 < b; j += 256) {
     float4 x[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) x[u] = __ldg(r4 + j + 32 * u);
@@ -96,30 +92,26 @@ __device__ __forceinline__ float warp_exact_sim(const float* __restrict__ row, c
       fma4x(x[u + 3], __ldg(q4 + j + 32 * (u + 3)), d3, n3);
     }
   }
-  for (; j + 96 < full4; j += 128) {
+  for (; j + 96 < b; j += 128) {
     const float4 x0 = __ldg(r4 + j), x1 = __ldg(r4 + j + 32), x2 = __ldg(r4 + j + 64), x3 = __ldg(r4 + j + 96);
-    const float4 y0 = __ldg(q4 + j), y1 = __ldg(q4 + j + 32), y2 = __ldg(q4 + j + 64), y3 = __ldg(q4 + j + 96);
-    fma4x(x0, y0, d0, n0);
-    fma4x(x1, y1, d1, n1);
-    fma4x(x2, y2, d2, n2);
-    fma4x(x3, y3, d3, n3);
+    fma4x(x0, __ldg(q4 + j), d0, n0);
+    fma4x(x1, __ldg(q4 + j + 32), d1, n1);
+    fma4x(x2, __ldg(q4 + j + 64), d2, n2);
+    fma4x(x3, __ldg(q4 + j + 96), d3, n3);
   }
-  for (; j < full4; j += 32) fma4x(__ldg(r4 + j), __ldg(q4 + j), d0, n0);
-  if (lane == 0) {  // the last, partial float4 of a dim that is not a multiple of 4 (the query's pad is not ours)
-    for (int i = full4 * 4; i < dim; ++i) {
-      const float x = __ldg(row + i);
-      d1 = fmaf(x, __ldg(q + i), d1);
-      n1 = fmaf(x, x, n1);
-    }
-  }
+  for (; j < b; j += 32) fma4x(__ldg(r4 + j), __ldg(q4 + j), d0, n0);
   float dot = (d0 + d1) + (d2 + d3), nn = (n0 + n1) + (n2 + n3);
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) {
     dot += __shfl_xor_sync(kFull, dot, off);
     nn += __shfl_xor_sync(kFull, nn, off);
   }
-  return dot * rsqrtf(fmaxf(nn, kEps * kEps)) * inv_qn;
+  dot_out = dot;
+  nn_out = nn;
 }
+
+constexpr int kRowsPerPass = 64;  // rows re-scored between two block barriers
+constexpr int kMaxSegs = 16;      // a row is split into <= 16 segments of >= 4 KB, one warp per segment at a time
 
 __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   extern __shared__ __align__(16) unsigned char smem6[];
@@ -128,6 +120,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   __shared__ u64 exact[kBandCap];             // their exact keys
   __shared__ u64 outk[32];
   __shared__ unsigned hist[256];
+  __shared__ float pd[kRowsPerPass][kMaxSegs], pn[kRowsPerPass][kMaxSegs];   // per (row, segment) partial sums
   __shared__ unsigned sel_prefix, sel_want, n_keys;
   __shared__ int band_cnt, bad;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -221,23 +214,58 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   const float* q = p.q + (size_t)b * p.q_ld;
   const float inv_qn = p.inv_qn[b];
 
-  // re-score band[from, to) into exact[from, to): one row per warp at a time
+  // Re-score band[from, to) into exact[from, to).  A row is cut into segments of >= 4 KB and the block's 8 warps
+  // take (row, segment) pairs round robin, so that even a handful of 16 KB rows keeps every warp loading (one
+  // warp per row left most of the block idle: 100 us per launch at 1M x 4096).  The per-segment partial sums are
+  // added up in segment order by one thread per row, so the result does not depend on which warp did what: the
+  // same formula as the single-query kernel, x.q * rsqrt(max(|x|^2, eps^2)) * (1 / max(|q|, eps))  (:61).
+  const int full4 = p.dim >> 2;  // float4s that lie entirely inside the descriptor
+  int seg_f4 = 256;
+  while ((full4 + seg_f4 - 1) / seg_f4 > kMaxSegs) seg_f4 *= 2;
+  const int segs = full4 > 0 ? (full4 + seg_f4 - 1) / seg_f4 : 1;
   auto rescore = [&](int from, int to) {
-    for (int j = from + warp; j < to; j += W6) {
-      const uint32_t row = key_row(band[j]);
-      if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
+    for (int r0 = from; r0 < to; r0 += kRowsPerPass) {
+      const int nr = to - r0 < kRowsPerPass ? to - r0 : kRowsPerPass;
+      for (int s_ = warp; s_ < nr * segs; s_ += W6) {
+        const int r = s_ / segs, c = s_ - r * segs;
+        const uint32_t row = key_row(band[r0 + r]);
+        float dot = 0.f, nn = 0.f;
+        if ((long long)row < p.n) {
+          const float* rp = p.db + (size_t)row * p.ld;
+          const int a = c * seg_f4, e = (c + 1) * seg_f4 < full4 ? (c + 1) * seg_f4 : full4;
+          warp_partial(reinterpret_cast<const float4*>(rp), reinterpret_cast<const float4*>(q), a, e, lane, dot, nn);
+          if (c == segs - 1) {  // the last, partial float4 of a dim that is not a multiple of 4 (the query's pad is not ours)
+            for (int i = full4 * 4; i < p.dim; ++i) {
+              const float x = __ldg(rp + i);
+              dot = fmaf(x, __ldg(q + i), dot);
+              nn = fmaf(x, x, nn);
+            }
+          }
+        }
         if (lane == 0) {
-          exact[j] = 0ull;
+          pd[r][c] = dot;
+          pn[r][c] = nn;
+        }
+      }
+      __syncthreads();
+      if (tid < nr) {
+        const uint32_t row = key_row(band[r0 + tid]);
+        if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
+          exact[r0 + tid] = 0ull;
           bad = 1;
           if (p.stats) atomicAdd(p.stats + 7, 1ull);
+        } else {
+          float dot = 0.f, nn = 0.f;
+          for (int c = 0; c < segs; ++c) {
+            dot += pd[tid][c];
+            nn += pn[tid][c];
+          }
+          const float s_ = dot * rsqrtf(fmaxf(nn, kEps * kEps)) * inv_qn;
+          exact[r0 + tid] = make_key(s_, row);
+          if (!(s_ == s_)) bad = 1;
         }
-        continue;
       }
-      const float s = warp_exact_sim(p.db + (size_t)row * p.ld, q, p.dim, inv_qn, lane);
-      if (lane == 0) {
-        exact[j] = make_key(s, row);
-        if (!(s == s)) bad = 1;
-      }
+      __syncthreads();
     }
   };
 
@@ -360,6 +388,15 @@ cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
   p.debug = a.debug;
   const size_t smem = (size_t)a.parts * a.kl * 8;
   if (smem > 40 * 1024) return cudaErrorInvalidConfiguration;
+  // static (~16 KB) + dynamic shared memory exceeds the 48 KB a kernel gets without opting in once kl = 32
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(k6_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
   k6_kernel<<<(unsigned)a.B, W6 * 32, smem, stream>>>(p);
   count_launch();
   return cudaGetLastError();
