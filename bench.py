@@ -130,6 +130,8 @@ def cpu_torch_qps(rows, dim, batch, k, budget_s=12.0):
     tensors (what the reference class executes with its device forced to CPU), one query at a time like the
     reference's API, all intra-op threads torch has.  Bounded row sample, cost scaled linearly in rows."""
     import torch
+    if torch.get_num_threads() < (os.cpu_count() or 1):   # torchrun exports OMP_NUM_THREADS=1
+        torch.set_num_threads(os.cpu_count() or 1)
     sample_rows, db, qs = _cpu_sample(rows, dim, min(batch, 64))
     view = torch.from_numpy(db)
     tq = torch.from_numpy(qs)
@@ -739,12 +741,16 @@ def run_dense(ctx, name, rows, dim, batch, k, steps, warmup, cpu_budget=12.0, ov
         parity = rep.as_dict()
         ok = rep.ok
         if world > 1:
-            # the NCCL all-gather + K4 route must return the same bits as the peer-memory kernel
-            i2, s2 = m.search_batch_device(par_q, k, exchange="nccl")
-            i1, s1 = m.search_batch_device(par_q, k)
+            # the NCCL all-gather + K4 route must return the same bits as the peer-memory kernel, and a repeat of
+            # the timed step's batch the same bits as the timed step
+            qfull = qb[(steps - 1) % nb] if not single else par_q
+            i2, s2 = m.search_batch_device(qfull, k, exchange="nccl")
+            i1, s1 = m.search_batch_device(qfull, k)
             torch.cuda.synchronize()
-            same = bool(torch.equal(i1, i2) and torch.equal(s1, s2) and torch.equal(i1, par_idx)
-                        and torch.equal(s1, par_sim))
+            m.check_exchange()
+            npar_ = par_idx.shape[0]
+            same = bool(torch.equal(i1, i2) and torch.equal(s1, s2) and torch.equal(i1[:npar_], par_idx)
+                        and torch.equal(s1[:npar_], par_sim))
             flag = torch.tensor([1 if same else 0], device=dev)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             parity["peer_route_equals_nccl_route_bitwise"] = bool(int(flag.item()))

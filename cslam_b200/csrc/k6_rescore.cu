@@ -37,7 +37,7 @@
 namespace cslam {
 namespace {
 
-constexpr int W6 = 8;            // warps per CTA
+constexpr int W6 = 16;           // warps per CTA (2 CTAs per SM: every query of a 256-batch is resident at once)
 constexpr int kBandCap = 384;    // candidates one query may re-score before giving up
 
 struct K6Dev {
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   if (enough) {
     for (int pass = 0; pass < 4; ++pass) {
       const int shift = 24 - 8 * pass;
-      hist[tid] = 0u;   // W6 * 32 == 256 threads
+      if (tid < 256) hist[tid] = 0u;
       __syncthreads();
       const unsigned prefix = sel_prefix;
       // the similarities of a query's candidates share their leading bits, so nearly every key of a pass falls
