@@ -611,10 +611,13 @@ def run_dense(ctx, name, rows, dim, batch, k, steps, warmup, cpu_budget=12.0, ov
         extra = torch.rand((64, dim), generator=gq, device=dev, dtype=torch.float32)
         extra /= extra.norm(dim=1, keepdim=True)
 
+    last_block = [0]   # query block of the most recent device_step: its results are what out_idx / out_sim hold
+
     def device_step(i):
         if incremental:
             m.add_local_shard(extra[i % 64:i % 64 + 1])
         m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+        last_block[0] = i % nb
 
     # ---- device-resident leg: `value` (CUDA events around the K steps, nothing between the launches) ----
     for i in range(warmup):
@@ -686,7 +689,7 @@ def run_dense(ctx, name, rows, dim, batch, k, steps, warmup, cpu_budget=12.0, ov
         for j in range(par_q.shape[0]):
             m.search_batch_device(par_q[j:j + 1], k, par_idx[j:j + 1], par_sim[j:j + 1])
     else:
-        last = (steps - 1) % nb
+        last = last_block[0]
         npar = min(args.parity_queries, batch)
         par_q = qb[last][:npar].contiguous()
         par_idx, par_sim = out_idx[:npar].clone(), out_sim[:npar].clone()
@@ -743,7 +746,7 @@ def run_dense(ctx, name, rows, dim, batch, k, steps, warmup, cpu_budget=12.0, ov
         if world > 1:
             # the NCCL all-gather + K4 route must return the same bits as the peer-memory kernel, and a repeat of
             # the timed step's batch the same bits as the timed step
-            qfull = qb[(steps - 1) % nb] if not single else par_q
+            qfull = qb[last_block[0]] if not single else par_q
             i2, s2 = m.search_batch_device(qfull, k, exchange="nccl")
             i1, s1 = m.search_batch_device(qfull, k)
             torch.cuda.synchronize()
