@@ -94,6 +94,8 @@ struct cslam_nns_s {
   DevBuf screen_stats;             // [2] u64: queries screened / handed to the 3xTF32 fallback
   bool screen = true;              // screening route enabled (CSLAM_NNS_SCREEN=0 or cslam_nns_set_screen disable it)
   long long screen_min_rows = 8192;  // below this the second and third launch cost more than the 3xTF32 pass saves
+  int seed_stride = 32;              // the screening pass is seeded from every seed_stride-th row (<= 1: no seeding)
+  long long seed_min_rows = 200000;  // ... when the database has at least this many rows
   PinBuf res_host;
   // integer row identities for the device-side candidate filter (cslam_nns_search_filtered)
   Arena ids_arena;
@@ -394,6 +396,42 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       }
       a.screen = true;
       a.k = kl;
+      // Seed the pass with a bound from a SAMPLE: the same kernel over every S-th row (a tensor map with S times
+      // the row pitch) and a select of the kl-th largest screened similarity per query.  Without it every one of
+      // the 2 * 74 lists of a query warms up on its own, ~kl * ln(rows per list / kl) insertions, each a lane-
+      // divergent round in the epilogue: ~0.3 ms per launch whatever the database size, i.e. most of a shard's
+      // kernel on 8 GPUs.  With the bound of a 1/S sample only the ~S * kl best rows of a query ever enter a list.
+      if (h->seed_stride > 1 && h->n >= h->seed_min_rows) {
+        K2Args sa = a;
+        sa.n = (h->n + h->seed_stride - 1) / h->seed_stride;
+        sa.ld = a.ld * h->seed_stride;
+        sa.gthr_plane = kQParGthrFull;   // zero (k2_prepare); cleared again by the seed kernel for the fallback pass
+        e = k2_launch(sa, h->num_sms, stream, &kerr);
+        if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (sample)", e);
+        DBG_SYNC(h, stream, "after the sample pass");
+        K6Args sr;
+        sr.db = a.db;
+        sr.n = sa.n;
+        sr.ld = sa.ld;
+        sr.dim = a.dim;
+        sr.q = qc;
+        sr.q_ld = (int)q_ld;
+        sr.qpar = a.inv_qn;
+        sr.part_keys = a.part_keys;
+        sr.parts = k2_parts(sa.n, Bc, h->dim, h->num_sms);
+        sr.B = Bc;
+        sr.k = k_run;
+        sr.kl = kl;
+        sr.out_keys = nullptr;
+        sr.out_idx = nullptr;
+        sr.out_sim = nullptr;
+        sr.idx_stride = 1;
+        sr.idx_offset = 0;
+        sr.stats = nullptr;
+        sr.seed = true;
+        CK(h, k6_rescore(sr, stream));
+        DBG_SYNC(h, stream, "after the seed kernel");
+      }
       {
         KernelTimer kt(h, stream);
         e = k2_launch(a, h->num_sms, stream, &kerr);
@@ -426,6 +464,7 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       if (env_int("CSLAM_NNS_SCREEN_NOFB", 0)) continue;   // development: leave the screening pass's lists in place
       a.screen = false;
       a.k = k_run;
+      a.gthr_plane = kQParGthrFull;
       a.active_mask = tail;
       a.active_count = tail + 8;
       e = k2_launch(a, h->num_sms, stream, &kerr);
@@ -530,6 +569,8 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->chain_enabled = env_int("CSLAM_NNS_CHAIN", 1) != 0;
   h->screen = env_int("CSLAM_NNS_SCREEN", 1) != 0;
   h->screen_min_rows = env_int("CSLAM_NNS_SCREEN_MIN_ROWS", 8192);
+  h->seed_stride = env_int("CSLAM_NNS_SEED_STRIDE", 32);
+  h->seed_min_rows = env_int("CSLAM_NNS_SEED_MIN_ROWS", 200000);
   *out = h;
   if (dim > 0) {
     int rc = cslam_nns_set_dim(h, dim);

@@ -602,8 +602,7 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
   p.q_mean = a.inv_qn + kQParMean * a.B;
   // zeroed by k2_prepare; the masked fallback pass has its own plane (the screening pass's bounds are bounds
   // of the SCREENED similarities and are still needed by k6_rescore's proof when the fallback runs)
-  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn)) +
-           (a.active_mask ? kQParGthrFull : kQParGthr) * a.B;
+  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn)) + a.gthr_plane * a.B;
   p.active_mask = a.active_mask;
   p.active_count = a.active_count;
   p.part_keys = a.part_keys;

@@ -59,6 +59,9 @@ struct K6Dev {
   unsigned* fail_count;
   unsigned long long* stats;
   int kl;  // capacity of the screening pass's lists (>= k)
+  int seed;            // seed mode: see K6Args
+  unsigned* gthr_w;    // seed mode: bound plane of the first pass (written) ...
+  unsigned* gthr_clr;  // ... and of the sample pass (cleared)
   u64* debug;  // development: 64 words per query (top-k keys by s~, counters), or null
 };
 
@@ -131,7 +134,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     bad = 0;
     n_keys = 0u;
     sel_prefix = 0u;
-    sel_want = (unsigned)k;
+    sel_want = (unsigned)(p.seed ? kl : k);
     if (b == 0 && p.stats) atomicAdd(p.stats, (unsigned long long)p.B);
   }
   if (tid < 32) outk[tid] = 0ull;
@@ -152,7 +155,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     if (saw_nan) bad = 1;  // NaN similarities sort first in the reference: left to the 3xTF32 pass
   }
   __syncthreads();
-  const bool enough = n_keys >= (unsigned)k;
+  const bool enough = n_keys >= (unsigned)(p.seed ? kl : k);
 
   // ---- 2. T = the k-th largest screened similarity of the union (as an ordered uint): radix select, 8 bits per
   //         pass, most significant first (a shared-memory histogram; thread 0 walks the 256 bins) ----------------------
@@ -208,6 +211,15 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
       }
       __syncthreads();
     }
+  }
+  if (p.seed) {
+    // the kl-th largest screened similarity of a SAMPLE of the rows: kl real rows reach it, so no row below it can
+    // be among any list's kl best of the full pass, which starts with this bound instead of an empty one
+    if (tid == 0) {
+      if (enough && sel_prefix != 0xffffffffu) p.gthr_w[b] = sel_prefix;
+      p.gthr_clr[b] = 0u;
+    }
+    return;
   }
   const float E = p.ebound[b];
   const unsigned T = sel_prefix;
@@ -386,6 +398,10 @@ cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
   p.stats = a.stats;
   p.kl = a.kl;
   p.debug = a.debug;
+  p.seed = a.seed ? 1 : 0;
+  p.gthr_w = reinterpret_cast<unsigned*>(const_cast<float*>(a.qpar)) + kQParGthr * a.B;
+  p.gthr_clr = reinterpret_cast<unsigned*>(const_cast<float*>(a.qpar)) + kQParGthrFull * a.B;
+  if (a.seed) p.gthr = p.gthr_clr;
   const size_t smem = (size_t)a.parts * a.kl * 8;
   if (smem > 40 * 1024) return cudaErrorInvalidConfiguration;
   // static (~16 KB) + dynamic shared memory exceeds the 48 KB a kernel gets without opting in once kl = 32

@@ -85,6 +85,10 @@ struct K6Args {
   long long idx_stride, idx_offset;
   unsigned long long* stats;  // [0] += queries screened, [1] += queries handed to the fallback
   u64* debug = nullptr;       // development: 64 words per query
+  // seed mode (the lists come from a screening pass over every S-th row): write the kl-th largest screened
+  // similarity of the union — a lower bound of the query's kl-th best over the WHOLE database, since the sample's
+  // rows are real rows — into the first pass's bound plane, clear the sample pass's plane, and do nothing else
+  bool seed = false;
 };
 cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream);
 // the per-query shared threshold plane the query-major batched kernel leaves behind ([B] ordered uints inside
@@ -127,6 +131,7 @@ struct K2Args {
   bool screen = false;
   const unsigned* active_mask = nullptr;
   const unsigned* active_count = nullptr;
+  int gthr_plane = kQParGthr;  // which plane of the parameter block holds this pass's shared k-th-best bounds
 };
 bool k2_supported(int B, int k, int dim);
 // number of partial key lists [parts][B][k] a launch for batch B writes (sizes part_keys, feeds k4_merge)

@@ -444,7 +444,7 @@ def test_save_load_refuses_pickle_by_default_and_data_setter(M, tmp_path):
 
 # ---- both batched tilings on every shape --------------------------------------------------------------
 
-@pytest.mark.parametrize("route", ["qm", "rows", "qm_noscreen", "qm_screen_all"])
+@pytest.mark.parametrize("route", ["qm", "rows", "qm_noscreen", "qm_screen_all", "qm_seeded"])
 def test_both_batched_kernels_on_all_shapes(route):
     """The router (k2_qm.cu: q_route) normally sends small batches (<= 96 queries, fewer at small
     dimensions) to the row-major kernel and the rest to the query-major CTA-pair kernel; here each kernel is forced (the switch is read once per process,
@@ -463,6 +463,8 @@ def test_both_batched_kernels_on_all_shapes(route):
         env["CSLAM_NNS_SCREEN"] = "0"
     elif route == "qm_screen_all":  # the screening route (one product + exact re-scoring) on EVERY shape,
         env["CSLAM_NNS_SCREEN_MIN_ROWS"] = "0"   # also n < 256, k = 32, dim not a multiple of 4 or 32
+    elif route == "qm_seeded":      # ... and with the bound seeded from a pass over every 4th row on every shape
+        env.update(CSLAM_NNS_SCREEN_MIN_ROWS="0", CSLAM_NNS_SEED_MIN_ROWS="0", CSLAM_NNS_SEED_STRIDE="4")
     out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "k2_check.py")] + shapes, env=env,
                          capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "K2 CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

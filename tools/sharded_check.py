@@ -27,8 +27,9 @@ def main():
     dist.init_process_group("nccl")
     dev = torch.device("cuda", torch.cuda.current_device())
     bad = 0
+    big = [(10_000_000, 256, [(256, 10), (256, 32)])] if os.environ.get("SHARDED_CHECK_BIG") else []
     for n, d, shapes in [(20011, 256, [(256, 10), (37, 1), (1, 32), (256, 10)]),
-                         (300000, 512, [(256, 10), (16, 10)])]:
+                         (300000, 512, [(256, 10), (16, 10), (256, 32)])] + big:
         db = synth.unit_rows(7 + n, n, d)
         peer = ShardedNearestNeighborsMatching(exchange="peer")
         nccl = ShardedNearestNeighborsMatching(exchange="nccl")
@@ -49,15 +50,28 @@ def main():
             if not same:
                 detail += " [rank %d peer!=nccl: %d idx, %d sims differ]" % (
                     rank, int((ia != ib).sum()), int((sa != sb).sum()))
+            note = ""
             if rank == 0:
                 wi, ws = whole._search_block(q, k)
                 pi, ps = ia.cpu().numpy(), sa.cpu().numpy()
                 if not (np.array_equal(wi, pi) and np.array_equal(ws, ps)):
-                    same = False
-                    j = int(np.argmax((wi != pi).any(axis=1) | (ws != ps).any(axis=1)))
-                    detail += " [peer!=unsharded: %d idx, %d sims differ, max |dsim| %.3g; q%d whole %s %s peer %s %s]" % (
-                        int((wi != pi).sum()), int((ws != ps).sum()), float(np.abs(ws - ps).max()), j,
-                        wi[j].tolist(), ws[j].tolist(), pi[j].tolist(), ps[j].tolist())
+                    # The shards and the whole database may be served by different routes (screening + exact fp32
+                    # re-scoring above 8192 rows, 3xTF32 below; single-query kernel for B = 1): then the
+                    # similarities agree to fp32 rounding instead of bit for bit, and rows may swap only where
+                    # two similarities tie within the tolerance.
+                    close = np.allclose(ws, ps, rtol=1e-5, atol=2e-6)
+                    ties = True
+                    for j, i in zip(*np.nonzero(wi != pi)):
+                        ties = ties and abs(float(ws[j, i]) - float(ps[j, i])) <= 1e-5 * abs(float(ws[j, i])) + 2e-6
+                    if close and ties:
+                        note = " (vs unsharded: equal to fp32 rounding, max |dsim| %.2g, %d rows swapped at ties)" % (
+                            float(np.abs(ws - ps).max()), int((wi != pi).sum()))
+                    else:
+                        same = False
+                        j = int(np.argmax((wi != pi).any(axis=1) | (np.abs(ws - ps) > 2e-6).any(axis=1)))
+                        detail += " [peer!=unsharded: %d idx, %d sims differ, max |dsim| %.3g; q%d whole %s %s peer %s %s]" % (
+                            int((wi != pi).sum()), int((ws != ps).sum()), float(np.abs(ws - ps).max()), j,
+                            wi[j].tolist(), ws[j].tolist(), pi[j].tolist(), ps[j].tolist())
             if detail:
                 print(detail, flush=True)
             ok = torch.tensor([1 if (same and used_peer) else 0], device=dev)
@@ -78,9 +92,9 @@ def main():
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 times.append(float(t.item()))
             if rank == 0:
-                print("n=%d d=%d B=%d k=%d world=%d: %s   step %.4f ms peer-memory kernel, %.4f ms all-gather + K4"
-                      % (n, d, B, k, world, "identical" if int(ok.item()) else "MISMATCH", times[0], times[1]),
-                      flush=True)
+                print("n=%d d=%d B=%d k=%d world=%d: %s%s   step %.4f ms peer-memory kernel, %.4f ms all-gather + K4"
+                      % (n, d, B, k, world, "peer == nccl bitwise" if int(ok.item()) else "MISMATCH", note or
+                         " == unsharded bitwise", times[0], times[1]), flush=True)
             bad += 0 if int(ok.item()) else 1
         del peer, nccl, whole
     if rank == 0:
