@@ -94,8 +94,10 @@ struct cslam_nns_s {
   DevBuf screen_stats;             // [2] u64: queries screened / handed to the 3xTF32 fallback
   bool screen = true;              // screening route enabled (CSLAM_NNS_SCREEN=0 or cslam_nns_set_screen disable it)
   long long screen_min_rows = 8192;  // below this the second and third launch cost more than the 3xTF32 pass saves
-  int seed_stride = 32;              // the screening pass is seeded from every seed_stride-th row (<= 1: no seeding)
+  int seed_stride = 0;               // the screening pass is seeded from every seed_stride-th row (0: sized by seed_rows)
+  long long seed_rows = 6000;        // rows of the seeding sample (about 1.5 list lengths per list of the sample pass)
   long long seed_min_rows = 200000;  // ... when the database has at least this many rows
+  long long seed_max_dim = 1024;     // ... and rows this short (the warm-up hides under the products of longer rows)
   PinBuf res_host;
   // integer row identities for the device-side candidate filter (cslam_nns_search_filtered)
   Arena ids_arena;
@@ -401,10 +403,14 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       // the 2 * 74 lists of a query warms up on its own, ~kl * ln(rows per list / kl) insertions, each a lane-
       // divergent round in the epilogue: ~0.3 ms per launch whatever the database size, i.e. most of a shard's
       // kernel on 8 GPUs.  With the bound of a 1/S sample only the ~S * kl best rows of a query ever enter a list.
-      if (h->seed_stride > 1 && h->n >= h->seed_min_rows) {
+      // The sample itself must not pay that warm-up: it is sized so that each of its lists sees only about
+      // 1.5 kl rows (seed_rows rows in all), where filling a list is all that happens.  Short rows only: with
+      // long rows (dim > 1024) a tile's products take far longer than its epilogue and the warm-up is hidden.
+      long long stride = h->seed_stride > 0 ? h->seed_stride : h->n / h->seed_rows;
+      if (stride > 1 && h->n >= h->seed_min_rows && h->dim <= h->seed_max_dim) {
         K2Args sa = a;
-        sa.n = (h->n + h->seed_stride - 1) / h->seed_stride;
-        sa.ld = a.ld * h->seed_stride;
+        sa.n = (h->n + stride - 1) / stride;
+        sa.ld = a.ld * (int)stride;
         sa.gthr_plane = kQParGthrFull;   // zero (k2_prepare); cleared again by the seed kernel for the fallback pass
         e = k2_launch(sa, h->num_sms, stream, &kerr);
         if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (sample)", e);
@@ -569,7 +575,9 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->chain_enabled = env_int("CSLAM_NNS_CHAIN", 1) != 0;
   h->screen = env_int("CSLAM_NNS_SCREEN", 1) != 0;
   h->screen_min_rows = env_int("CSLAM_NNS_SCREEN_MIN_ROWS", 8192);
-  h->seed_stride = env_int("CSLAM_NNS_SEED_STRIDE", 32);
+  h->seed_stride = env_int("CSLAM_NNS_SEED_STRIDE", 0);
+  h->seed_rows = env_int("CSLAM_NNS_SEED_ROWS", 6000);
+  h->seed_max_dim = env_int("CSLAM_NNS_SEED_MAX_DIM", 1024);
   h->seed_min_rows = env_int("CSLAM_NNS_SEED_MIN_ROWS", 200000);
   *out = h;
   if (dim > 0) {

@@ -464,7 +464,8 @@ def test_both_batched_kernels_on_all_shapes(route):
     elif route == "qm_screen_all":  # the screening route (one product + exact re-scoring) on EVERY shape,
         env["CSLAM_NNS_SCREEN_MIN_ROWS"] = "0"   # also n < 256, k = 32, dim not a multiple of 4 or 32
     elif route == "qm_seeded":      # ... and with the bound seeded from a pass over every 4th row on every shape
-        env.update(CSLAM_NNS_SCREEN_MIN_ROWS="0", CSLAM_NNS_SEED_MIN_ROWS="0", CSLAM_NNS_SEED_STRIDE="4")
+        env.update(CSLAM_NNS_SCREEN_MIN_ROWS="0", CSLAM_NNS_SEED_MIN_ROWS="0", CSLAM_NNS_SEED_STRIDE="4",
+                   CSLAM_NNS_SEED_MAX_DIM="100000")
     out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "k2_check.py")] + shapes, env=env,
                          capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "K2 CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
