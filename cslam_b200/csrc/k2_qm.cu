@@ -177,18 +177,25 @@ __device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq,
     if (key <= st.min_key) return st;
     lst[st.min_pos * BM] = key;
   }
-  u64 mk = ~0ull;
-  int mp = 0;
+  // the new smallest entry: four independent compare chains (entries j, j + 1, j + 2, j + 3 mod 4) and a
+  // three-compare combine.  One chain over all k entries is k dependent 64-bit compare-and-select steps,
+  // ~500 cycles at k = 24, and this function IS the cost of a list's warm-up.
+  u64 mk0 = ~0ull, mk1 = ~0ull, mk2 = ~0ull, mk3 = ~0ull;
+  int mp0 = 0, mp1 = 1, mp2 = 2, mp3 = 3;
   for (int j = 0; j < k; j += 4) {
     const u64 e0 = lst[j * BM];
     const u64 e1 = j + 1 < k ? lst[(j + 1) * BM] : ~0ull;
     const u64 e2 = j + 2 < k ? lst[(j + 2) * BM] : ~0ull;
     const u64 e3 = j + 3 < k ? lst[(j + 3) * BM] : ~0ull;
-    if (e0 < mk) { mk = e0; mp = j; }
-    if (e1 < mk) { mk = e1; mp = j + 1; }
-    if (e2 < mk) { mk = e2; mp = j + 2; }
-    if (e3 < mk) { mk = e3; mp = j + 3; }
+    if (e0 < mk0) { mk0 = e0; mp0 = j; }
+    if (e1 < mk1) { mk1 = e1; mp1 = j + 1; }
+    if (e2 < mk2) { mk2 = e2; mp2 = j + 2; }
+    if (e3 < mk3) { mk3 = e3; mp3 = j + 3; }
   }
+  if (mk1 < mk0) { mk0 = mk1; mp0 = mp1; }
+  if (mk3 < mk2) { mk2 = mk3; mp2 = mp3; }
+  const u64 mk = mk2 < mk0 ? mk2 : mk0;
+  const int mp = mk2 < mk0 ? mp2 : mp0;
   st.min_key = mk;
   st.min_pos = mp;
   // the list is full: its smallest entry is a proven lower bound of the query's final k-th best
