@@ -148,7 +148,8 @@ struct TopState {
   float thr;      // similarity below which a candidate cannot matter: max(own smallest entry once the list
                   // is full, best bound published by any list of this query)
   float thr_u;    // the same bound for u = s / inv|q| (saves a multiply per column), 2^-21 slack
-  unsigned g_seen;  // last published bound seen (ordered uint)
+  unsigned g_seen;  // best bound known to this list: its own smallest entry once full, or a published one (ordered uint)
+  unsigned dirty;   // g_seen comes from this list and has not been published yet (the caller does, once per tile)
 };
 __device__ __forceinline__ void top_set_threshold(TopState& st, float thr, float invq) {
   st.thr = thr;
@@ -200,9 +201,11 @@ __device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq,
   st.min_pos = mp;
   // the list is full: its smallest entry is a proven lower bound of the query's final k-th best
   const unsigned ord = (unsigned)(mk >> 32);
+  // (published by the caller at the end of the tile: 2 x 74 lists raising their bounds entry by entry during
+  // the warm-up are thousands of atomics on ONE word per query, which the L2 serialises)
   if (ord > st.g_seen && ord != 0xffffffffu) {  // NaN entries are never a bound
-    if (gthr) atomicMax(gthr, ord);
     st.g_seen = ord;
+    st.dirty = gthr != nullptr ? 1u : 0u;
     top_set_threshold(st, key_sim(mk), invq);
   }
   return st;
@@ -436,6 +439,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     ts.thr = -INFINITY;
     ts.thr_u = -INFINITY;
     ts.g_seen = 0u;
+    ts.dirty = 0u;
     // Grid-wide threshold sharing.  The 2 x 74 lists of a query each warm up from nothing; whenever one of
     // them is full its smallest entry is a proven lower bound of the query's final k-th best (k real rows
     // at or above it exist), so it is published with one atomicMax (inside offer_key) and every list of the
@@ -504,6 +508,10 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
                               : 0ull;
           ts = offer_key(lst, p.k, key, invq_r, gq, ts);
         }
+      }
+      if (ts.dirty) {  // this list's bound grew during the tile: one atomic per list and tile at most
+        atomicMax(gq, ts.g_seen);
+        ts.dirty = 0u;
       }
       if (p.prof) wscan += clock64() - tscan0;
       tc_fence_before();
