@@ -76,7 +76,7 @@ __host__ __device__ inline QSmem qcarve(int k, int stages) {
   s.q_lo_off = 3 * s.tile_bytes;
   s.stage_bytes = (SCREEN ? 2 : 4) * s.tile_bytes;  // 16 KB (BK = 32) or 8 KB (BK = 16) per tile: multiple of 1024
   uint32_t o = s.stage_bytes * (uint32_t)stages;
-  s.lists_off = o;  o += 2u * BM * k * 8;              // [2 column halves][k][128] keys
+  s.lists_off = o;  o += 2u * BM * (k + 4) * 8;        // [2 column halves][k entries + 4 group minima][128] keys
   s.norm_off = o;   o += 2u * 2u * BN2 * 4;            // [2 accumulators][inv|x| (256), sum(x) (256)]
   s.bars_off = o;   o += (4u * kMaxStages + 10u) * 8;
   s.tmem_off = o;   o += 16;
@@ -143,7 +143,7 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)
 // out-of-line call (inlining the insertion 32x per chunk blew the epilogue up to ~15k instructions and the
 // instruction cache with it: C5 went from 5.9 to 15.5 ms).
 struct TopState {
-  int cnt, min_pos;
+  int cnt, min_pos, min_grp;
   u64 min_key;
   float thr;      // similarity below which a candidate cannot matter: max(own smallest entry once the list
                   // is full, best bound published by any list of this query)
@@ -168,41 +168,73 @@ __device__ __forceinline__ uint32_t select32(const uint32_t (&v)[32], int j) {
   const uint32_t d0 = (j & 8) ? c[1] : c[0], d1 = (j & 8) ? c[3] : c[2];
   return (j & 16) ? d1 : d0;
 }
+// Smallest entry of lst[lo .. hi) and its position (entries are [j * BM] apart).
+__device__ __forceinline__ void group_min(const u64* lst, int lo, int hi, u64& mk, int& mp) {
+  mk = ~0ull;
+  mp = lo;
+  for (int j = lo; j < hi; ++j) {
+    const u64 e = lst[j * BM];
+    if (e < mk) {
+      mk = e;
+      mp = j;
+    }
+  }
+}
 // Called by all 32 lanes together, each with its own list and candidate (key 0 = nothing to offer).
-__device__ __noinline__ TopState offer_key(u64* lst, int k, u64 key, float invq, unsigned* gthr, TopState st) {
+// The list is an UNSORTED set of k keys cut into 4 groups of gs = ceil(k / 4) entries whose smallest entries are
+// kept behind it (lst[(k + g) * BM]).  Replacing the list's smallest entry re-scans ONE group and compares four
+// cached minima: ~80 instructions, where a re-scan of all k entries cost ~400 (k = 24) — and this function is
+// what a list's warm-up costs: k ln(rows / k) replacements, each a lane-divergent round of the epilogue.
+__device__ __noinline__ TopState offer_key(u64* lst, int k, int gs, u64 key, float invq, unsigned* gthr, TopState st) {
   if (key == 0ull) return st;
+  u64* gm = lst + (size_t)k * BM;
+  u64 mk;
   if (st.cnt < k) {
     lst[st.cnt * BM] = key;
     if (++st.cnt < k) return st;
+    // the list has just filled up: all four group minima from scratch
+    mk = ~0ull;
+    for (int g = 0; g < 4; ++g) {
+      const int lo = g * gs, hi = (g + 1) * gs < k ? (g + 1) * gs : k;
+      u64 m;
+      int mp;
+      group_min(lst, lo < k ? lo : k, hi, m, mp);   // an empty group (small k) keeps the sentinel and never wins
+      gm[g * BM] = m;
+      if (m < mk) {
+        mk = m;
+        st.min_pos = mp;
+        st.min_grp = g;
+      }
+    }
   } else {
     if (key <= st.min_key) return st;
     lst[st.min_pos * BM] = key;
+    const int g = st.min_grp;
+    const int lo = g * gs, hi = (g + 1) * gs < k ? (g + 1) * gs : k;
+    u64 mg;
+    int mpg;
+    group_min(lst, lo, hi, mg, mpg);
+    gm[g * BM] = mg;
+    const u64 m0 = g == 0 ? mg : gm[0], m1 = g == 1 ? mg : gm[BM], m2 = g == 2 ? mg : gm[2 * BM],
+              m3 = g == 3 ? mg : gm[3 * BM];
+    const u64 a = m1 < m0 ? m1 : m0, b = m3 < m2 ? m3 : m2;
+    const int ga = m1 < m0 ? 1 : 0, gb = m3 < m2 ? 3 : 2;
+    mk = b < a ? b : a;
+    const int bg = b < a ? gb : ga;
+    if (bg == g) {
+      st.min_pos = mpg;
+    } else {  // the smallest entry now sits in another group: find where
+      const int lo2 = bg * gs, hi2 = (bg + 1) * gs < k ? (bg + 1) * gs : k;
+      u64 m_;
+      group_min(lst, lo2, hi2, m_, st.min_pos);
+      st.min_grp = bg;
+    }
   }
-  // the new smallest entry: four independent compare chains (entries j, j + 1, j + 2, j + 3 mod 4) and a
-  // three-compare combine.  One chain over all k entries is k dependent 64-bit compare-and-select steps,
-  // ~500 cycles at k = 24, and this function IS the cost of a list's warm-up.
-  u64 mk0 = ~0ull, mk1 = ~0ull, mk2 = ~0ull, mk3 = ~0ull;
-  int mp0 = 0, mp1 = 1, mp2 = 2, mp3 = 3;
-  for (int j = 0; j < k; j += 4) {
-    const u64 e0 = lst[j * BM];
-    const u64 e1 = j + 1 < k ? lst[(j + 1) * BM] : ~0ull;
-    const u64 e2 = j + 2 < k ? lst[(j + 2) * BM] : ~0ull;
-    const u64 e3 = j + 3 < k ? lst[(j + 3) * BM] : ~0ull;
-    if (e0 < mk0) { mk0 = e0; mp0 = j; }
-    if (e1 < mk1) { mk1 = e1; mp1 = j + 1; }
-    if (e2 < mk2) { mk2 = e2; mp2 = j + 2; }
-    if (e3 < mk3) { mk3 = e3; mp3 = j + 3; }
-  }
-  if (mk1 < mk0) { mk0 = mk1; mp0 = mp1; }
-  if (mk3 < mk2) { mk2 = mk3; mp2 = mp3; }
-  const u64 mk = mk2 < mk0 ? mk2 : mk0;
-  const int mp = mk2 < mk0 ? mp2 : mp0;
   st.min_key = mk;
-  st.min_pos = mp;
   // the list is full: its smallest entry is a proven lower bound of the query's final k-th best
-  const unsigned ord = (unsigned)(mk >> 32);
   // (published by the caller at the end of the tile: 2 x 74 lists raising their bounds entry by entry during
   // the warm-up are thousands of atomics on ONE word per query, which the L2 serialises)
+  const unsigned ord = (unsigned)(mk >> 32);
   if (ord > st.g_seen && ord != 0xffffffffu) {  // NaN entries are never a bound
     st.g_seen = ord;
     st.dirty = gthr != nullptr ? 1u : 0u;
@@ -240,7 +272,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
   uint64_t* norm_bar = acc_full + 4;             // [2] local: all 256 rows' norms are in (8 converter warps)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L.tmem_off);
 
-  for (int i = tid; i < 2 * BM * p.k; i += kThreads) lists[i] = 0ull;
+  for (int i = tid; i < 2 * BM * (p.k + 4); i += kThreads) lists[i] = 0ull;
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -428,13 +460,15 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     const float qmean_r = valid ? p.q_mean[q] : 0.f;
     const float invq_r = valid ? p.inv_qn[q] : 0.f;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-    u64* lst = lists + (size_t)eh * BM * p.k + tq;
+    u64* lst = lists + (size_t)eh * BM * (p.k + 4) + tq;
+    const int gs = (p.k + 3) >> 2;   // entries per group of the list (offer_key)
     // Thread-private UNSORTED top-k: the first k candidates fill the list, after that a candidate replaces
     // the smallest entry and the minimum is re-found with k independent loads (a sorted list costs a
     // dependent load-compare-store chain per shifted entry; K4 does not need sorted parts).
     TopState ts;
     ts.cnt = 0;
     ts.min_pos = 0;
+    ts.min_grp = 0;
     ts.min_key = 0ull;
     ts.thr = -INFINITY;
     ts.thr_u = -INFINITY;
@@ -506,7 +540,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           const u64 key = (has && !(s_ < ts.thr))
                               ? (((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)))
                               : 0ull;
-          ts = offer_key(lst, p.k, key, invq_r, gq, ts);
+          ts = offer_key(lst, p.k, gs, key, invq_r, gq, ts);
         }
       }
       if (ts.dirty) {  // this list's bound grew during the tile: one atomic per list and tile at most
