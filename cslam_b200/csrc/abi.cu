@@ -95,7 +95,7 @@ struct cslam_nns_s {
   bool screen = true;              // screening route enabled (CSLAM_NNS_SCREEN=0 or cslam_nns_set_screen disable it)
   long long screen_min_rows = 8192;  // below this the second and third launch cost more than the 3xTF32 pass saves
   int seed_stride = 0;               // the screening pass is seeded from every seed_stride-th row (0: sized by seed_rows)
-  long long seed_rows = 6000;        // rows of the seeding sample (about 1.5 list lengths per list of the sample pass)
+  long long seed_rows = 15000;       // rows of the seeding sample
   long long seed_min_rows = 200000;  // ... when the database has at least this many rows
   long long seed_max_dim = 1024;     // ... and rows this short (the warm-up hides under the products of longer rows)
   PinBuf res_host;
@@ -403,12 +403,16 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       // the 2 * 74 lists of a query warms up on its own, ~kl * ln(rows per list / kl) insertions, each a lane-
       // divergent round in the epilogue: ~0.3 ms per launch whatever the database size, i.e. most of a shard's
       // kernel on 8 GPUs.  With the bound of a 1/S sample only the ~S * kl best rows of a query ever enter a list.
-      // The sample itself must not pay that warm-up: it is sized so that each of its lists sees only about
-      // 1.5 kl rows (seed_rows rows in all), where filling a list is all that happens.  Short rows only: with
+      // The sample is small (seed_rows rows in all) so that its own warm-up stays cheap.  Short rows only: with
       // long rows (dim > 1024) a tile's products take far longer than its epilogue and the warm-up is hidden.
-      long long stride = h->seed_stride > 0 ? h->seed_stride : h->n / h->seed_rows;
+      long long stride = h->seed_stride > 0 ? h->seed_stride : (h->seed_rows > 0 ? h->n / h->seed_rows : 0);
       if (stride > 1 && h->n >= h->seed_min_rows && h->dim <= h->seed_max_dim) {
+        // The sample pass keeps short lists (8 entries): with no bound to start from, every column of its first
+        // tile is a candidate until a list is full, and a full list of 8 starts rejecting three times sooner than
+        // one of 24.  The seed is still the kl-th largest similarity of the union of those lists.
+        const int kls = kl < 8 ? kl : 8;
         K2Args sa = a;
+        sa.k = kls;
         sa.n = (h->n + stride - 1) / stride;
         sa.ld = a.ld * (int)stride;
         sa.gthr_plane = kQParGthrFull;   // zero (k2_prepare); cleared again by the seed kernel for the fallback pass
@@ -426,8 +430,8 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
         sr.part_keys = a.part_keys;
         sr.parts = k2_parts(sa.n, Bc, h->dim, h->num_sms);
         sr.B = Bc;
-        sr.k = k_run;
-        sr.kl = kl;
+        sr.k = kl;        // rank of the seed: the kl-th largest screened similarity of the sample
+        sr.kl = kls;      // capacity of the sample pass's lists
         sr.out_keys = nullptr;
         sr.out_idx = nullptr;
         sr.out_sim = nullptr;
@@ -576,7 +580,7 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->screen = env_int("CSLAM_NNS_SCREEN", 1) != 0;
   h->screen_min_rows = env_int("CSLAM_NNS_SCREEN_MIN_ROWS", 8192);
   h->seed_stride = env_int("CSLAM_NNS_SEED_STRIDE", 0);
-  h->seed_rows = env_int("CSLAM_NNS_SEED_ROWS", 6000);
+  h->seed_rows = env_int("CSLAM_NNS_SEED_ROWS", 15000);
   h->seed_max_dim = env_int("CSLAM_NNS_SEED_MAX_DIM", 1024);
   h->seed_min_rows = env_int("CSLAM_NNS_SEED_MIN_ROWS", 200000);
   *out = h;

@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     bad = 0;
     n_keys = 0u;
     sel_prefix = 0u;
-    sel_want = (unsigned)(p.seed ? kl : k);
+    sel_want = (unsigned)k;   // seed mode: k is the rank of the seed (the full pass's list length)
     if (b == 0 && p.stats) atomicAdd(p.stats, (unsigned long long)p.B);
   }
   if (tid < 32) outk[tid] = 0ull;
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     if (saw_nan) bad = 1;  // NaN similarities sort first in the reference: left to the 3xTF32 pass
   }
   __syncthreads();
-  const bool enough = n_keys >= (unsigned)(p.seed ? kl : k);
+  const bool enough = n_keys >= (unsigned)k;
 
   // ---- 2. T = the k-th largest screened similarity of the union (as an ordered uint): radix select, 8 bits per
   //         pass, most significant first (a shared-memory histogram; thread 0 walks the 256 bins) ----------------------
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
 }  // namespace
 
 cudaError_t k6_rescore(const K6Args& a, cudaStream_t stream) {
-  if (a.B <= 0 || a.k <= 0 || a.k > 32 || a.kl < a.k || a.kl > 32) return cudaErrorInvalidValue;
+  if (a.B <= 0 || a.k <= 0 || a.k > 32 || a.kl <= 0 || a.kl > 32 || (!a.seed && a.kl < a.k)) return cudaErrorInvalidValue;
   K6Dev p;
   p.db = a.db;
   p.n = a.n;
