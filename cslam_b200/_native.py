@@ -56,6 +56,8 @@ SIGNATURES = {
     "cslam_nns_set_screen": (_c.c_int, [_handle, _c.c_int, _i64]),
     "cslam_nns_screen_stats": (_c.c_int, [_handle, _c.POINTER(_i64), _c.POINTER(_i64)]),
     "cslam_nns_debug_copy": (_c.c_int, [_handle, _c.c_int, _c.c_void_p, _i64]),
+    "cslam_nns_search_static": (_c.c_int, [_c.c_int, _f32p, _i64, _i64, _i64, _f32p, _c.c_int, _i64p, _f32p,
+                                            _c.c_void_p, _c.c_char_p, _i64]),
     "cslam_nns_time_search": (_c.c_int, [_handle, _f32p, _i64, _i64, _c.c_int, _c.c_int,
                                          _c.c_void_p, _c.POINTER(_c.c_float)]),
 }

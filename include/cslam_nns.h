@@ -196,6 +196,29 @@ int cslam_nns_search_sharded(cslam_nns_t h, cslam_nns_xchg_t x, const float* que
                              int src_is_device, int k, int rank, int world, int phase,
                              int64_t* out_idx_dev, float* out_sim_dev, void* stream);
 
+/* -- single-query search that allocates nothing (NO counterpart in the reference)
+ *    ---------------------------------------------------------------------------------------- */
+#define CSLAM_NNS_STATIC_MAX_K 32      /* largest k of cslam_nns_search_static */
+#define CSLAM_NNS_STATIC_MAX_CTAS 512  /* CTAs (= SMs of the device) its scratch is sized for */
+/* For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it): the k most similar rows of a CALLER-OWNED device database for one query, by the same single-query
+ * kernel as cslam_nns_search(B = 1), with the kernel's scratch (a 256-byte ticket block + 512 x 32 packed keys,
+ * ~129 KB) in a file-scope `static __device__` array instead of handle-owned buffers.  No handle; the call makes no
+ * cudaMalloc / cudaFree / allocating library call.  Every GPU that loads the library holds the array until exit.
+ *   db_dev: n rows of dim fp32 values, row pitch ld floats (0 = dim; >= dim, multiple of 4; the floats
+ *   [dim, ld) of every row must be zero), 16-byte aligned, on `device`; query_dev: dim fp32 values, 16-byte aligned;
+ *   out_idx_dev / out_sim_dev: k entries each in device memory (either may be NULL); entries [min(k, n), k) get
+ *   -1 / -inf.  Stream-ordered on `stream`, no host synchronisation.
+ * Limits (CSLAM_NNS_EINVAL with a message naming the limit otherwise): 1 <= k <= CSLAM_NNS_STATIC_MAX_K,
+ * 1 <= n <= 2^32 - 2, a device with at most CSLAM_NNS_STATIC_MAX_CTAS SMs.
+ * The array is SHARED by every call on the device and keeps the last call's contents (the call clears the part
+ * that must start at zero on `stream` first): calls whose kernels can overlap on the GPU — different streams, or
+ * concurrent host threads on different streams — RACE on it; order them on one stream or with events.
+ * err / err_len (optional): receives a NUL-terminated message on failure. */
+int cslam_nns_search_static(int device, const float* db_dev, int64_t n, int64_t ld, int64_t dim,
+                             const float* query_dev, int k, int64_t* out_idx_dev, float* out_sim_dev,
+                             void* stream, char* err, int64_t err_len);
+
 /* -- tuning / diagnostics ----------------------------------------------------------------------- */
 
 /* Force a search variant for tests and profiling: 0 = automatic, 1 = single-query kernel looped,
