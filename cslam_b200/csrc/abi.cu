@@ -95,7 +95,7 @@ struct cslam_nns_s {
   bool screen = true;              // screening route enabled (CSLAM_NNS_SCREEN=0 or cslam_nns_set_screen disable it)
   long long screen_min_rows = 8192;  // below this the second and third launch cost more than the 3xTF32 pass saves
   int seed_stride = 0;               // the screening pass is seeded from every seed_stride-th row (0: sized by seed_rows)
-  long long seed_rows = 15000;       // rows of the seeding sample
+  long long seed_rows = 0;           // rows of the seeding sample (0: sized from the database, see search_device)
   long long seed_min_rows = 200000;  // ... when the database has at least this many rows
   long long seed_max_dim = 1024;     // ... and rows this short (the warm-up hides under the products of longer rows)
   PinBuf res_host;
@@ -405,17 +405,25 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       // kernel on 8 GPUs.  With the bound of a 1/S sample only the ~S * kl best rows of a query ever enter a list.
       // The sample is small (seed_rows rows in all) so that its own warm-up stays cheap.  Short rows only: with
       // long rows (dim > 1024) a tile's products take far longer than its epilogue and the warm-up is hidden.
-      long long stride = h->seed_stride > 0 ? h->seed_stride : (h->seed_rows > 0 ? h->n / h->seed_rows : 0);
+      // Sample size: one 256-row tile per CTA pair (18 944 rows) up to 2.5M rows, up to four for larger databases
+      // (10M x 256: 2.95 ms per batch with one tile, 2.84 with four, no better with eight; 1.25M x 256: one is best).
+      long long tiles_per_pair = h->n / 2500000;
+      tiles_per_pair = tiles_per_pair < 1 ? 1 : (tiles_per_pair > 4 ? 4 : tiles_per_pair);
+      const long long sample_rows = h->seed_rows > 0 ? h->seed_rows : 18944 * tiles_per_pair;
+      long long stride = h->seed_stride > 0 ? h->seed_stride : h->n / sample_rows;
       if (stride > 1 && h->n >= h->seed_min_rows && h->dim <= h->seed_max_dim) {
-        // The sample pass keeps short lists (8 entries): with no bound to start from, every column of its first
-        // tile is a candidate until a list is full, and a full list of 8 starts rejecting three times sooner than
-        // one of 24.  The seed is still the kl-th largest similarity of the union of those lists.
-        const int kls = kl < 8 ? kl : 8;
+        // The sample pass keeps ONE entry per list — the best row of the 128 columns a thread sees — and shares no
+        // bound between lists: with nothing to start from, every column of a list's first tile is a candidate until
+        // the list is full, and one convergent insertion round per column made the sample pass cost 52 us of
+        // epilogue for 2.6 us of products (lists of 8; role profile, 1.25M x 256).  The 2 * pairs maxima belong to
+        // distinct rows, so their kl-th largest is reached by kl real rows: a valid seed, and nearly as tight as the
+        // kl-th largest of the whole sample (its best kl rows mostly fall into different lists).
+        const int kls = 1;
         K2Args sa = a;
         sa.k = kls;
         sa.n = (h->n + stride - 1) / stride;
         sa.ld = a.ld * (int)stride;
-        sa.gthr_plane = kQParGthrFull;   // zero (k2_prepare); cleared again by the seed kernel for the fallback pass
+        sa.gthr_plane = -1;              // lists of the sample pass do not publish or read a shared bound
         e = k2_launch(sa, h->num_sms, stream, &kerr);
         if (e != cudaSuccess) return fail_cuda(h, kerr ? kerr : "k2_launch (sample)", e);
         DBG_SYNC(h, stream, "after the sample pass");
@@ -580,7 +588,7 @@ int cslam_nns_create(int device, int64_t dim, int64_t initial_capacity, cslam_nn
   h->screen = env_int("CSLAM_NNS_SCREEN", 1) != 0;
   h->screen_min_rows = env_int("CSLAM_NNS_SCREEN_MIN_ROWS", 8192);
   h->seed_stride = env_int("CSLAM_NNS_SEED_STRIDE", 0);
-  h->seed_rows = env_int("CSLAM_NNS_SEED_ROWS", 15000);
+  h->seed_rows = env_int("CSLAM_NNS_SEED_ROWS", 0);
   h->seed_max_dim = env_int("CSLAM_NNS_SEED_MAX_DIM", 1024);
   h->seed_min_rows = env_int("CSLAM_NNS_SEED_MIN_ROWS", 200000);
   *out = h;

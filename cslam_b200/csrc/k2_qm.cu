@@ -479,7 +479,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     // at or above it exist), so it is published with one atomicMax (inside offer_key) and every list of the
     // query — full or not — drops candidates below the best bound published so far (read once per tile).
     // This removes most of the k ln(rows/k) insertions per list, which diverge lane by lane.
-    unsigned* gq = (valid && !(p.dbg & 64)) ? p.gthr + q : nullptr;
+    unsigned* gq = (valid && p.gthr != nullptr && !(p.dbg & 64)) ? p.gthr + q : nullptr;
     long long wepi = 0, wnorm = 0, wfence = 0, wscan = 0;
     for (long long t = 0; t < my_tiles; ++t) {
       const int a = (int)(t & 1);
@@ -540,7 +540,18 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           const u64 key = (has && !(s_ < ts.thr))
                               ? (((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)))
                               : 0ull;
+          const float thr_was = ts.thr_u;
           ts = offer_key(lst, p.k, gs, key, invq_r, gq, ts);
+          // A list whose bound has just moved re-tests its remaining survivors at once: the mask above was built
+          // with the bound the chunk started with, and while a list fills up or warms up that bound is far too
+          // low — every remaining column then cost a round of its own (the whole first tile of a list: 128 rounds;
+          // the seeding sample pass, one tile per list, spent 20 us there for 2.6 us of products).
+          if (__any_sync(kFull, ts.thr_u != thr_was)) {
+            uint32_t keep = 0u;
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj) keep |= !(__uint_as_float(v[jj]) < ts.thr_u) ? (1u << jj) : 0u;
+            m &= keep;
+          }
         }
       }
       if (ts.dirty) {  // this list's bound grew during the tile: one atomic per list and tile at most
@@ -651,7 +662,8 @@ cudaError_t qlaunch(const K2Args& a, int num_sms, cudaStream_t stream, const cha
   p.q_mean = a.inv_qn + kQParMean * a.B;
   // zeroed by k2_prepare; the masked fallback pass has its own plane (the screening pass's bounds are bounds
   // of the SCREENED similarities and are still needed by k6_rescore's proof when the fallback runs)
-  p.gthr = reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn)) + a.gthr_plane * a.B;
+  p.gthr = a.gthr_plane < 0 ? nullptr   // no bound sharing between the lists (the seeding sample pass)
+                            : reinterpret_cast<unsigned*>(const_cast<float*>(a.inv_qn)) + a.gthr_plane * a.B;
   p.active_mask = a.active_mask;
   p.active_count = a.active_count;
   p.part_keys = a.part_keys;

@@ -39,6 +39,7 @@ namespace {
 
 constexpr int W6 = 16;           // warps per CTA (2 CTAs per SM: every query of a 256-batch is resident at once)
 constexpr int kBandCap = 384;    // candidates one query may re-score before giving up
+constexpr int kKeysPerThread = 10;   // the union of a query's lists: <= 148 parts x 32 entries = 4736 keys <= 512 x 10
 
 struct K6Dev {
   const float* db;
@@ -76,59 +77,144 @@ __device__ __forceinline__ void fma4x(const float4& x, const float4& q, float& d
   nn = fmaf(x.w, x.w, nn);
 }
 
-// Partial sums x.q and |x|^2 of one database row over the float4 range [a, b), computed by a whole warp (every lane
-// returns the warp's totals).  8 independent 16-byte row loads per lane are in flight (4 KB per warp): the rows are
-// scattered over the database, so this kernel lives on memory-level parallelism; the query comes out of L1.
-__device__ __forceinline__ void warp_partial(const float4* __restrict__ r4, const float4* __restrict__ q4, int a,
-                                             int b, int lane, float& dot_out, float& nn_out) {
-  float d0 = 0.f, n0 = 0.f, d1 = 0.f, n1 = 0.f, d2 = 0.f, n2 = 0.f, d3 = 0.f, n3 = 0.f;
-  int j = a + lane;
-  for (; j + 224 < b; j += 256) {
-    float4 x[8];
+constexpr int kRowsPerPass = 64;  // rows re-scored between two block barriers
+constexpr int kMaxSegs = 16;      // warps that share one row (a row is spread over 32 .. 512 threads)
+
+// Re-score `nr` candidates (keys cand[0 .. nr), nr <= kRowsPerPass) exactly; partial sums go to pd / pn, one entry per
+// (row, warp of the row's thread group), and are added up in warp order by the caller.
+//
+// Work layout: the block's 512 threads are cut into groups of G = 2^g_log2 threads (32 <= G <= 512, G >= the row's
+// float4 count when that is <= 512); thread `sub` of a group owns the float4 columns sub, sub + G, ... (NQ of
+// them per chunk of G * NQ columns) of EVERY row its group re-scores, so its slice of the query stays in registers,
+// and a group takes the rows grp, grp + groups, ... UR = 8 / NQ at a time: 8 independent 16-byte loads per thread
+// are in flight whatever the row length (64 KB per block).  The version this replaced gave (row, 4 KB segment)
+// pairs to warps one after the other and re-read the query with every row: 3 round trips for the first 10 rows
+// of a 1M x 4096 search, 11 us where the loads themselves need ~2.
+template <int NQ>
+__device__ __forceinline__ void rescore_pass(const K6Dev& p, const float* __restrict__ q, const u64* cand, int nr,
+                                             int g_log2, float (*pd)[kMaxSegs], float (*pn)[kMaxSegs]) {
+  constexpr int UR = NQ == 1 ? 4 : 8 / NQ;   // NQ == 1 (rows up to 2 KB): groups are narrow and many, 4 rows each is plenty
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int G = 1 << g_log2, sub = tid & (G - 1), grp = tid >> g_log2, groups = (W6 * 32) >> g_log2;
+  const int wig = (tid >> 5) & ((G >> 5) - 1);   // warp within the group
+  const int full4 = p.dim >> 2;                  // float4s that lie entirely inside the descriptor
+  const int span = G * NQ;
+  const float4* q4 = reinterpret_cast<const float4*>(q);
+  const bool one_chunk = full4 <= span;
+  float4 qv[NQ];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) x[u] = __ldg(r4 + j + 32 * u);
+  for (int j = 0; j < NQ; ++j) {
+    const int c = sub + j * G;
+    qv[j] = c < full4 ? __ldg(q4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int i0 = 0; (i0 * groups + grp) < nr; i0 += UR) {
+    const float4* rp[UR];
+    bool ok[UR];
+    float dot[UR], nn[UR];
 #pragma unroll
-    for (int u = 0; u < 8; u += 4) {
-      fma4x(x[u + 0], __ldg(q4 + j + 32 * (u + 0)), d0, n0);
-      fma4x(x[u + 1], __ldg(q4 + j + 32 * (u + 1)), d1, n1);
-      fma4x(x[u + 2], __ldg(q4 + j + 32 * (u + 2)), d2, n2);
-      fma4x(x[u + 3], __ldg(q4 + j + 32 * (u + 3)), d3, n3);
+    for (int u = 0; u < UR; ++u) {
+      const int r = (i0 + u) * groups + grp;
+      const uint32_t row = r < nr ? key_row(cand[r]) : 0xffffffffu;
+      ok[u] = (long long)row < p.n;   // never follow a row number the database does not have
+      rp[u] = reinterpret_cast<const float4*>(p.db + (size_t)(ok[u] ? row : 0u) * p.ld);
+      dot[u] = 0.f;
+      nn[u] = 0.f;
+    }
+    for (int c0 = 0; c0 < full4 || c0 == 0; c0 += span) {
+      if (!one_chunk) {
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) {
+          const int c = c0 + sub + j * G;
+          qv[j] = c < full4 ? __ldg(q4 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      float4 x[UR][NQ];
+#pragma unroll
+      for (int u = 0; u < UR; ++u)
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) {
+          const int c = c0 + sub + j * G;
+          x[u][j] = (ok[u] && c < full4) ? __ldg(rp[u] + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+      for (int u = 0; u < UR; ++u)
+#pragma unroll
+        for (int j = 0; j < NQ; ++j) fma4x(x[u][j], qv[j], dot[u], nn[u]);
+      if (full4 == 0) break;
+    }
+    if (sub == 0 && (p.dim & 3)) {  // the last, partial float4 of a dim that is not a multiple of 4
+#pragma unroll
+      for (int u = 0; u < UR; ++u)
+        if (ok[u]) {
+          const float* rf = reinterpret_cast<const float*>(rp[u]);
+          for (int i = full4 * 4; i < p.dim; ++i) {
+            const float xv = __ldg(rf + i);
+            dot[u] = fmaf(xv, __ldg(q + i), dot[u]);
+            nn[u] = fmaf(xv, xv, nn[u]);
+          }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < UR; ++u) {
+      float d = dot[u], n = nn[u];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        d += __shfl_xor_sync(kFull, d, off);
+        n += __shfl_xor_sync(kFull, n, off);
+      }
+      const int r = (i0 + u) * groups + grp;
+      if (lane == 0 && r < nr) {
+        pd[r][wig] = d;
+        pn[r][wig] = n;
+      }
     }
   }
-  for (; j + 96 < b; j += 128) {
-    const float4 x0 = __ldg(r4 + j), x1 = __ldg(r4 + j + 32), x2 = __ldg(r4 + j + 64), x3 = __ldg(r4 + j + 96);
-    fma4x(x0, __ldg(q4 + j), d0, n0);
-    fma4x(x1, __ldg(q4 + j + 32), d1, n1);
-    fma4x(x2, __ldg(q4 + j + 64), d2, n2);
-    fma4x(x3, __ldg(q4 + j + 96), d3, n3);
-  }
-  for (; j < b; j += 32) fma4x(__ldg(r4 + j), __ldg(q4 + j), d0, n0);
-  float dot = (d0 + d1) + (d2 + d3), nn = (n0 + n1) + (n2 + n3);
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    dot += __shfl_xor_sync(kFull, dot, off);
-    nn += __shfl_xor_sync(kFull, nn, off);
-  }
-  dot_out = dot;
-  nn_out = nn;
 }
 
-constexpr int kRowsPerPass = 64;  // rows re-scored between two block barriers
-constexpr int kMaxSegs = 16;      // a row is split into <= 16 segments of >= 4 KB, one warp per segment at a time
+// One instance of the largest value held in v[0 .. N) of the warp's lanes is removed and returned (0 when the warp
+// holds nothing any more).  Values are ordered-uint similarities, 0 = empty.
+template <int N>
+__device__ __forceinline__ unsigned warp_pop_max(unsigned (&v)[N], int lane) {
+  unsigned lm = 0u;
+#pragma unroll
+  for (int u = 0; u < N; ++u) lm = v[u] > lm ? v[u] : lm;
+  const unsigned m = __reduce_max_sync(kFull, lm);
+  if (m == 0u) return 0u;
+  const unsigned has = __ballot_sync(kFull, lm == m);
+  if (lane == __ffs(has) - 1) {
+    bool done = false;
+#pragma unroll
+    for (int u = 0; u < N; ++u)
+      if (!done && v[u] == m) {
+        v[u] = 0u;
+        done = true;
+      }
+  }
+  return m;
+}
 
-__global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
+__device__ __forceinline__ unsigned long long k6_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void __launch_bounds__(W6 * 32, 2) k6_kernel(const K6Dev p) {
   extern __shared__ __align__(16) unsigned char smem6[];
   u64* keys = reinterpret_cast<u64*>(smem6);  // the union of this query's lists: [parts * kl]
   __shared__ u64 band[kBandCap];              // candidates to re-score
   __shared__ u64 exact[kBandCap];             // their exact keys
   __shared__ u64 outk[32];
-  __shared__ unsigned hist[256];
+  __shared__ unsigned wtop[W6 * 32];          // [warp][r]: the warp's r-th largest screened similarity
   __shared__ float pd[kRowsPerPass][kMaxSegs], pn[kRowsPerPass][kMaxSegs];   // per (row, segment) partial sums
   __shared__ unsigned sel_prefix, sel_want, n_keys;
   __shared__ int band_cnt, bad;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x, k = p.k, kl = p.kl;
   const int total = p.parts * kl;
+  unsigned long long ts[6] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull};   // development trace (p.debug): phase time stamps
+  const bool trace = p.debug != nullptr && tid == 0;
+  if (trace) ts[0] = k6_now();
   if (tid == 0) {
     band_cnt = 0;
     bad = 0;
@@ -138,6 +224,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     if (b == 0 && p.stats) atomicAdd(p.stats, (unsigned long long)p.B);
   }
   if (tid < 32) outk[tid] = 0ull;
+  wtop[tid] = 0u;
   __syncthreads();
 
   // ---- 1. the union of the lists -> shared memory ------------------------------------------------------------------
@@ -156,61 +243,35 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   }
   __syncthreads();
   const bool enough = n_keys >= (unsigned)k;
+  if (trace) ts[1] = k6_now();
 
-  // ---- 2. T = the k-th largest screened similarity of the union (as an ordered uint): radix select, 8 bits per
-  //         pass, most significant first (a shared-memory histogram; thread 0 walks the 256 bins) ----------------------
+  // ---- 2. T = the k-th largest screened similarity of the union (as an ordered uint; equal values count once
+  //         each).  Every warp pops the k largest of the <= 10 values per lane it holds (one REDUX per pop), warp 0
+  //         pops the k largest of those 16 * k.  (Four radix passes over a shared-memory histogram took 7 us of
+  //         a 15 us launch at 1.25M x 256.) -------------------------------------------------------------------------
   if (enough) {
-    for (int pass = 0; pass < 4; ++pass) {
-      const int shift = 24 - 8 * pass;
-      if (tid < 256) hist[tid] = 0u;
-      __syncthreads();
-      const unsigned prefix = sel_prefix;
-      // the similarities of a query's candidates share their leading bits, so nearly every key of a pass falls
-      // into the same bin: the lanes of a warp that hit the same bin are counted with ONE shared-memory atomic
-      // (match.any), otherwise the 3 500 same-address atomics of a pass serialise
-      for (int base = 0; base < total; base += W6 * 32) {
-        const int i = base + tid;
-        unsigned bin = 0xffffffffu;
-        if (i < total) {
-          const u64 key = keys[i];
-          const unsigned ord = (unsigned)(key >> 32);
-          if (key != 0ull && (pass == 0 || (ord >> (shift + 8)) == prefix)) bin = (ord >> shift) & 255u;
-        }
-        const unsigned peers = __match_any_sync(kFull, bin);
-        if (bin != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
-      }
-      __syncthreads();
-      if (warp == 0) {
-        // walk the 256 bins from the top until `want` keys are covered: lane l owns bins 255 - 8l .. 248 - 8l
-        // (a serial walk by one thread cost ~20 us per query: 1000 dependent shared-memory loads)
-        const unsigned want = sel_want;
-        unsigned c[8], mine = 0u;
+    unsigned v[kKeysPerThread];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          c[u] = hist[255 - 8 * lane - u];
-          mine += c[u];
-        }
-        unsigned incl = mine;  // inclusive prefix over lanes 0..lane (bins 255 .. 248 - 8 lane)
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-          const unsigned o = __shfl_up_sync(kFull, incl, off);
-          if (lane >= off) incl += o;
-        }
-        const unsigned hit = __ballot_sync(kFull, incl >= want);   // never empty: `enough` keys exist
-        const int owner = hit ? __ffs(hit) - 1 : 31;
-        if (lane == owner) {
-          unsigned acc = incl - mine;   // keys in the bins above this lane's
-          int u = 0;
-          for (; u < 7; ++u) {
-            if (acc + c[u] >= want) break;
-            acc += c[u];
-          }
-          sel_want = want - acc;                                   // rank of the k-th largest inside the chosen bin
-          sel_prefix = (prefix << 8) | (unsigned)(255 - 8 * lane - u);
-        }
-      }
-      __syncthreads();
+    for (int u = 0; u < kKeysPerThread; ++u) {
+      const int i = tid + u * (W6 * 32);
+      v[u] = i < total ? (unsigned)(keys[i] >> 32) : 0u;
     }
+    const unsigned want = sel_want;   // k (seed mode: the rank of the seed)
+    for (unsigned r = 0; r < want; ++r) {
+      const unsigned m = warp_pop_max(v, lane);
+      if (lane == 0) wtop[warp * 32 + r] = m;
+      if (m == 0u) break;   // this warp holds nothing more (the rest of its column was zeroed below)
+    }
+    __syncthreads();
+    if (warp == 0) {
+      unsigned w[W6];
+#pragma unroll
+      for (int u = 0; u < W6; ++u) w[u] = wtop[u * 32 + lane];   // lane r holds every warp's r-th largest
+      unsigned t = 0u;
+      for (unsigned r = 0; r < want; ++r) t = warp_pop_max(w, lane);
+      if (lane == 0) sel_prefix = t;   // 0 cannot happen: `enough` non-empty keys exist
+    }
+    __syncthreads();
   }
   if (p.seed) {
     // the kl-th largest screened similarity of a SAMPLE of the rows: kl real rows reach it, so no row below it can
@@ -221,54 +282,39 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     }
     return;
   }
+  if (trace) ts[2] = k6_now();
   const float E = p.ebound[b];
   const unsigned T = sel_prefix;
   const float* q = p.q + (size_t)b * p.q_ld;
   const float inv_qn = p.inv_qn[b];
 
-  // Re-score band[from, to) into exact[from, to).  A row is cut into segments of >= 4 KB and the block's 8 warps
-  // take (row, segment) pairs round robin, so that even a handful of 16 KB rows keeps every warp loading (one
-  // warp per row left most of the block idle: 100 us per launch at 1M x 4096).  The per-segment partial sums are
-  // added up in segment order by one thread per row, so the result does not depend on which warp did what: the
-  // same formula as the single-query kernel, x.q * rsqrt(max(|x|^2, eps^2)) * (1 / max(|q|, eps))  (:61).
-  const int full4 = p.dim >> 2;  // float4s that lie entirely inside the descriptor
-  int seg_f4 = 256;
-  while ((full4 + seg_f4 - 1) / seg_f4 > kMaxSegs) seg_f4 *= 2;
-  const int segs = full4 > 0 ? (full4 + seg_f4 - 1) / seg_f4 : 1;
+  // Re-score band[from, to) into exact[from, to): rescore_pass leaves per-(row, warp) partial sums, one thread per
+  // row adds them up in warp order, so the result does not depend on scheduling: the same formula as the
+  // single-query kernel, x.q * rsqrt(max(|x|^2, eps^2)) * (1 / max(|q|, eps))  (:61).
+  const int full4 = p.dim >> 2;
+  int g_log2 = 5;
+  while (g_log2 < 9 && (1 << g_log2) < full4) ++g_log2;        // threads per row: 32 .. 512
+  const int G = 1 << g_log2;
+  const int nq = full4 <= G ? 1 : (full4 <= 2 * G ? 2 : 4);   // float4 per thread and chunk (rows beyond 8192 floats: several chunks)
+  const int wpr = G >> 5;                                      // warps per row
   auto rescore = [&](int from, int to) {
     for (int r0 = from; r0 < to; r0 += kRowsPerPass) {
       const int nr = to - r0 < kRowsPerPass ? to - r0 : kRowsPerPass;
-      for (int s_ = warp; s_ < nr * segs; s_ += W6) {
-        const int r = s_ / segs, c = s_ - r * segs;
-        const uint32_t row = key_row(band[r0 + r]);
-        float dot = 0.f, nn = 0.f;
-        if ((long long)row < p.n) {
-          const float* rp = p.db + (size_t)row * p.ld;
-          const int a = c * seg_f4, e = (c + 1) * seg_f4 < full4 ? (c + 1) * seg_f4 : full4;
-          warp_partial(reinterpret_cast<const float4*>(rp), reinterpret_cast<const float4*>(q), a, e, lane, dot, nn);
-          if (c == segs - 1) {  // the last, partial float4 of a dim that is not a multiple of 4 (the query's pad is not ours)
-            for (int i = full4 * 4; i < p.dim; ++i) {
-              const float x = __ldg(rp + i);
-              dot = fmaf(x, __ldg(q + i), dot);
-              nn = fmaf(x, x, nn);
-            }
-          }
-        }
-        if (lane == 0) {
-          pd[r][c] = dot;
-          pn[r][c] = nn;
-        }
+      switch (nq) {
+        case 1: rescore_pass<1>(p, q, band + r0, nr, g_log2, pd, pn); break;
+        case 2: rescore_pass<2>(p, q, band + r0, nr, g_log2, pd, pn); break;
+        default: rescore_pass<4>(p, q, band + r0, nr, g_log2, pd, pn); break;
       }
       __syncthreads();
       if (tid < nr) {
         const uint32_t row = key_row(band[r0 + tid]);
-        if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass; never follow a bad row
+        if ((long long)row >= p.n) {  // cannot happen with lists written by the screening pass
           exact[r0 + tid] = 0ull;
           bad = 1;
           if (p.stats) atomicAdd(p.stats + 7, 1ull);
         } else {
           float dot = 0.f, nn = 0.f;
-          for (int c = 0; c < segs; ++c) {
+          for (int c = 0; c < wpr; ++c) {
             dot += pd[tid][c];
             nn += pn[tid][c];
           }
@@ -300,6 +346,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   __syncthreads();
   block_rank_select(exact, ntop, k, outk);   // outk[k - 1] = the k-th largest exact key so far
   __syncthreads();
+  if (trace) ts[3] = k6_now();
   const float l0 = ntop >= k ? key_sim(outk[k - 1]) : __int_as_float(0x7fc00000);
   const float lim = l0 - E;   // by (1) no row whose screened similarity is below lim can reach l0
   __syncthreads();            // everybody has read outk before it is cleared again below
@@ -320,6 +367,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
   const int m = nband < kBandCap ? nband : kBandCap;
   rescore(ntop, m);
   __syncthreads();
+  if (trace) ts[4] = k6_now();
 
   // ---- 5. the proof, or the fallback -------------------------------------------------------------------------------
   const unsigned g = __ldcg(p.gthr + b);
@@ -341,6 +389,7 @@ __global__ void __launch_bounds__(W6 * 32) k6_kernel(const K6Dev p) {
     d[54] = (u64)bad;
     d[55] = (u64)p.n;
     d[56] = (u64)total;
+    for (int j = 0; j < 5; ++j) d[59 + j] = ts[j];
   }
   if (!proven) {
     if (tid == 0) {
