@@ -12,6 +12,7 @@ one synchronisation) and ``search_candidates`` (search + the call
 min-gap filter on the device).
 """
 import ctypes
+import operator
 
 import numpy as np
 import torch
@@ -331,8 +332,38 @@ class NearestNeighborsMatching(object):
             queries = torch.from_numpy(np.asarray(queries).astype(np.float32))
         q = queries.reshape(-1, self.dim).to(torch.float32)
         idx, sims = self._search_block(q, k)
-        items = [[self.items[i] for i in row] for row in idx.tolist()]
-        return items, sims
+        return self._items_of(idx), sims
+
+    def _items_of(self, idx):
+        """(B, kk) rows -> list of B item lists: one C-level lookup of all B * kk rows (a Python-level loop over
+        2560 dict lookups costs more than the search of a small shard)."""
+        B, kk = idx.shape
+        flat = idx.ravel().tolist()
+        if len(flat) == 0:
+            return [[] for _ in range(B)]
+        if len(flat) == 1:
+            return [[self.items[flat[0]]]]
+        got = operator.itemgetter(*flat)(self.items)
+        return [list(got[i * kk:(i + 1) * kk]) for i in range(B)]
+
+    def search_batches(self, batches, k, depth=2):
+        """Additive API: a stream of host query blocks -> a generator of ``(items, sims)`` per block, in order,
+        with block i+1's upload and block i-1's result read overlapping block i's search (``pipeline.py``)."""
+        from .pipeline import pipelined_search
+        if self._h is None:
+            return iter([([], []) for _ in batches])
+
+        def search_device(dq, kk, out_idx, out_sim):
+            h = self._h
+            rc = h.lib.cslam_nns_search(h.h, dq.data_ptr(), int(dq.shape[0]), int(dq.shape[1]), 1, kk,
+                                        out_idx.data_ptr(), out_sim.data_ptr(), 1, _raw_stream(self._dev_index), None)
+            if rc:
+                _native.check(rc, h.h)
+
+        def items_of(rows):
+            return self._items_of(rows)
+
+        return pipelined_search(self, batches, int(k), depth, True, search_device, items_of, lambda: None)
 
     def _search_block(self, q, k):
         """q: (B, dim) fp32 torch tensor, host or device -> (idx[B,kk] int64, sims[B,kk] f32)."""

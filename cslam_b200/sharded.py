@@ -278,7 +278,27 @@ class ShardedNearestNeighborsMatching(object):
             return None, None
         idx, sims = idx.cpu().numpy(), sims.cpu().numpy()
         self._check_exchange()
-        return [[self.items[i] for i in row] for row in idx.tolist()], sims
+        return self._items_of(idx), sims
+
+    def _items_of(self, idx):
+        """(B, kk) global rows -> list of B item lists (the identity mapping needs no lookups)."""
+        if isinstance(self.items, RowIdentity):
+            return idx.tolist()
+        return [[self.items[i] for i in row] for row in idx.tolist()]
+
+    def search_batches(self, batches, k, root_only=False, depth=2):
+        """A stream of host query blocks -> a generator of ``(items, sims)``, one per block, in order: the
+        pipelined form of ``search_batch`` for callers that have the next block ready while the current one is
+        searched (message batches queued by the subscriber, a serving loop).  Every block still travels host ->
+        device and its results device -> host; block i+1's upload (own stream, own copy engine) and block i-1's
+        result read run while block i is searched, and up to ``depth`` blocks are in flight.  With several ranks
+        every rank passes the same blocks and uploads each whole block over its own PCIe link (no collective and
+        no SM use on the upload path: it has to run next to a kernel that occupies every SM).
+        ``root_only=True``: ranks other than 0 yield ``(None, None)`` and read nothing back."""
+        from .pipeline import pipelined_search
+        reads = not (root_only and self.rank != 0)
+        return pipelined_search(self, batches, int(k), depth, reads, self.search_batch_device, self._items_of,
+                                self._check_exchange)
 
     def search(self, query, k):
         if self.n == 0 and self.dim is None:

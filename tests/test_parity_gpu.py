@@ -491,3 +491,42 @@ def test_batched_nan_zero_and_duplicate_rows(M):
         assert items[j] == ref_items
         np.testing.assert_allclose(sims[j][1:], ref_sims[1:], rtol=RTOL, atol=ATOL)
     assert items[3][1:4] == [50, 100, 2000]                          # duplicates: lower row first
+
+
+@pytest.mark.gpu
+def test_search_batches_pipeline_equals_search_batch():
+    """The pipelined generator (uploads, searches and result reads of consecutive blocks overlapping) returns what
+    one synchronous search_batch per block returns — bitwise — for ragged block sizes, a reused matcher and an
+    early stop of the consumer; the sharded class (one rank) goes through the same pipeline."""
+    import numpy as np
+    import torch
+    import synth
+    from cslam_b200 import NearestNeighborsMatching
+    from cslam_b200.sharded import ShardedNearestNeighborsMatching
+    n, d, k = 30_000, 256, 10
+    db = synth.unit_rows(4242, n, d)
+    m = NearestNeighborsMatching()
+    m.add_items(db, [1000 + i for i in range(n)])
+    sizes = [256, 256, 64, 256, 1, 130, 256, 256]
+    blocks = [synth.queries_for(500 + j, db, b) for j, b in enumerate(sizes)]
+    want = [m.search_batch(b, k) for b in blocks]
+    for depth in (1, 2, 3):
+        got = list(m.search_batches(iter(blocks), k, depth=depth))
+        assert len(got) == len(want)
+        for (gi, gs), (wi, ws) in zip(got, want):
+            assert gi == wi and np.array_equal(gs, ws)
+    # pinned torch blocks, and a consumer that stops after two blocks; the matcher stays usable
+    pinned = [torch.from_numpy(b).pin_memory() for b in blocks]
+    gen = m.search_batches(iter(pinned), k)
+    first, second = next(gen), next(gen)
+    gen.close()
+    assert first[0] == want[0][0] and second[0] == want[1][0]
+    again = list(m.search_batches(iter(pinned[:3]), k))
+    assert [a[0] for a in again] == [w[0] for w in want[:3]]
+    # the sharded class with one rank
+    sm = ShardedNearestNeighborsMatching(dim=d)
+    sm.add_local_shard(torch.from_numpy(db).cuda())
+    sm.finalize_bulk()
+    got = list(sm.search_batches(iter(blocks), k))
+    for (gi, gs), (wi, ws) in zip(got, want):
+        assert np.array_equal(np.asarray(gi) + 1000, np.asarray(wi)) and np.array_equal(gs, ws)
