@@ -16,19 +16,27 @@
 // Tensor-bound: algorithmic flops per launch = 2 * n * dim * B (issued: 3x that).
 // Algorithmic HBM bytes per launch = n * ld * 4 (the DB is read exactly once per batch of <= 256).
 //
-// One persistent CTA per SM, tiles of 128 database rows, K blocks of 32 floats (one 128-byte
-// swizzle row).  Warp roles (320 threads):
-//   warps 0-3  epilogue   tcgen05.ld the accumulator (lane == database row), scale by the row's and
-//                         the query's inverse norms, compare against the per-query threshold and
-//                         queue the rare survivors; per-query sorted lists live in shared memory
-//   warps 4-7  converter  split each landed database tile: write x_hi back in place and x_lo to a
-//                         second tile at the same (swizzled) offsets, accumulate |x|^2 per row
-//   warp  8    producer   TMA (cp.async.bulk.tensor, 128B swizzle) of the raw database tile and of the
-//                         pre-split query tiles q_hi / q_lo into a multi-stage ring
-//   warp  9    MMA        one elected lane issues 3 x 4 tcgen05.mma per K block; tcgen05.commit frees
-//                         the ring slot / publishes the accumulator; owns the TMEM allocation
-// The accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps the
-// MMAs of tile i+1.
+// This file: the ROW-MAJOR one-CTA kernel for small batches (database rows on the MMA's M side, N = the batch
+// padded to 16, so tensor work scales with the batch and a small batch runs at HBM speed), k2_prepare (query
+// planes and per-query parameters, shared with the query-major pair kernel in k2_qm.cu) and the routing entry
+// k2_launch.  Large batches take k2_qm.cu (screening pass + k6_rescore.cu).
+//
+// One persistent CTA per SM, tiles of 128 database rows, K blocks of 32 floats (one 128-byte swizzle row).
+// Warp roles (512 threads):
+//   warps 0-3          epilogue   tcgen05.ld the accumulator (lane == database row), a branch-free pass over 16
+//                                 queries, barrier.red.or "did anything survive", owner warps insert the queued
+//                                 survivors into the per-query sorted lists; full lists publish their k-th best
+//   warps 4-7, 12-15   converter  two groups taking alternate K blocks: thread r owns tile row r, splits its 128
+//                                 bytes into x_hi / x_lo, accumulates |x|^2 and sum(x), and writes the split row
+//                                 with tcgen05.st into a ring of operand slots in TENSOR MEMORY (the split tiles
+//                                 never exist in shared memory)
+//   warp  8            producer   TMA (cp.async.bulk.tensor, 128B swizzle, evict-first) of the raw database tile
+//   warp  9            MMA        the whole warp runs the loop, elect.sync picks the lane that issues 3 x 4
+//                                 tcgen05.mma per K block with the A operand read from TMEM; tcgen05.commit frees
+//                                 the operand slot / publishes the accumulator; owns the TMEM allocation
+//   warp 10            Q producer both query planes of a K block as one 3-D TMA box (evict-last)
+// The accumulator is double-buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1.
+// Design history and measurements: DESIGN.md §3 "Row-major one-CTA kernel".
 #include <cuda.h>
 
 #include <cstdlib>
