@@ -613,10 +613,17 @@ def run_dense(ctx, name, rows, dim, batch, k, steps, warmup, cpu_budget=12.0, ov
 
     last_block = [0]   # query block of the most recent device_step: its results are what out_idx / out_sim hold
 
+    # one prepared call per query block (ShardedNearestNeighborsMatching.plan_search_device: pointers and shapes
+    # converted once), so that the Python loop can keep ahead of a 32 us kernel
+    plans = [m.plan_search_device(qb[j], k, out_idx, out_sim) for j in range(nb)] if world == 1 else None
+
     def device_step(i):
         if incremental:
             m.add_local_shard(extra[i % 64:i % 64 + 1])
-        m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
+        if plans is not None:
+            plans[i % nb]()
+        else:
+            m.search_batch_device(qb[i % nb], k, out_idx, out_sim)
         last_block[0] = i % nb
 
     # ---- device-resident leg: `value` (CUDA events around the K steps, nothing between the launches) ----

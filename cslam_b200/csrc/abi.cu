@@ -539,6 +539,7 @@ int stage_queries(cslam_nns_t h, const float* queries, long long B, long long q_
   CK(h, cudaMemcpy2DAsync(h->q.p, (size_t)pld * 4, queries, (size_t)q_ld * 4, (size_t)dim * 4,
                           (size_t)B, src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
                           stream));
+  h->k1_chain = false;  // the staging copy is an ordinary stream operation: the search starts after it, unchained
   *dq = (const float*)h->q.p;
   *dq_ld = pld;
   return 0;

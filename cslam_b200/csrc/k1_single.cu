@@ -64,7 +64,7 @@ struct K1Dev {
   float* out_sim;
   long long idx_stride, idx_offset;
   float* all_sims;
-  int dep_wait;            // execute griddepcontrol.wait once the ring is primed (chained searches, see k1_kernel)
+  int dep_wait;            // execute griddepcontrol.wait after the stream, before the tail (chained searches, see k1_kernel)
   unsigned* done_flag;     // mapped host word (or null): receives done_value after the results are written
   unsigned done_value;
   long long keep_rows;  // rows below this are loaded with L2 evict-last, the rest evict-first (0: no hints)
@@ -168,13 +168,6 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     }
   }
   K1_STAMP(tid == 0, 4);  // ring primed (mbarrier init + first S bulk copies issued)
-  // Chained searches of the SAME database (programmatic dependent launch): this grid's CTAs were scheduled as
-  // the previous search's CTAs left their SMs, and the first row tiles are already on their way — rows that
-  // only change through the library's own stream-ordered appends at the END of the database.  Everything else
-  // (the query, the ticket / scratch slot, the output) waits here until the previous grid has completed and
-  // flushed: what overlaps is the launch latency, the prologue and the first-byte latency, not the streams.
-  // A no-op for an ordinary launch.
-  if (p.dep_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
 #ifdef K1_PROF
   if (tid == 1 && my_items > 2) {  // a plain load from a part of the database nobody has touched yet
     const float4* far = p.db + ((gw + 2 * GW) * p.rows_per_tile) * p.ld4 + 8;
@@ -331,6 +324,16 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   }
   if (p.all_sims) return;
   K1_STAMP(tid == 0, 2);  // warp 0 of this CTA is through its share of the stream
+  // Chained searches of the SAME database (programmatic dependent launch): this grid's CTAs were scheduled as the
+  // previous search's CTAs left their SMs and have streamed their whole share of the database meanwhile.  Up to
+  // here the kernel has only READ — rows, which change only through the library's own stream-ordered appends at
+  // the END of the database (an append in between breaks the chain), and the query, which was complete before the
+  // previous search started (anything queued between the two searches also breaks the chain) — and written only
+  // shared memory and registers.  The ticket / scratch slot, the output and the done flag wait here until the
+  // previous grid has completed and flushed: what overlaps with its tail is this search's launch latency,
+  // prologue AND stream.  At most two searches are in flight (this grid's CTAs hold their SMs until the wait
+  // returns; the launcher chains only grids of one CTA per SM).  A no-op for an ordinary launch.
+  if (p.dep_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
 
   // -- k == 1: the best key of the grid is one atomicMax per CTA; the CTA that draws the last ticket
   //    decodes and publishes it.  No scratch lists, no second merge level. ------------------------------
@@ -627,7 +630,8 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   cudaLaunchAttribute attr[1];
   // A chained search of the same database needs every SM to hold exactly one CTA of the previous search (then at
   // most two searches are ever in flight and the ticket / scratch ring of 4 cannot wrap) and a scan long enough
-  // that the tiles fetched before griddepcontrol.wait are nowhere near the appended tail of the database.
+  // that the search is worth chaining at all (everything read before griddepcontrol.wait is rows [0, n) of this
+  // search's own row count: an append between two searches breaks the chain in abi.cu).
   const bool chain_ok = !a.dep_wait || (grid == num_sms && p.tiles_div >= 4 * (long long)p.stages);
   if (!chain_ok) p.dep_wait = 0;
   if (a.overlap_prev && chain_ok) {  // see the top of k1_kernel

@@ -36,8 +36,8 @@ struct K1Args {
   // scratch, ticket or output with this one (another database, cslam_nns_search_multi).
   bool overlap_prev = false;
   // with overlap_prev: the previous launch searched the SAME database (same handle): the kernel then waits for
-  // it (griddepcontrol.wait) right after priming its ring, before it touches the query, its ticket / scratch
-  // slot or the output.  false = independent databases (cslam_nns_search_multi): no wait at all.
+  // it (griddepcontrol.wait) after streaming its share of the rows and before it touches its ticket / scratch
+  // slot, the output or the done flag.  false = independent databases (cslam_nns_search_multi): no wait at all.
   bool dep_wait = false;
   // host destination: mapped pinned word that receives done_value once the results are written (k <= 32 only)
   unsigned* done_flag = nullptr;

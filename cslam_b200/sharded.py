@@ -236,6 +236,28 @@ class ShardedNearestNeighborsMatching(object):
         _native.check(rc, None)
         return out_idx, out_sim
 
+    def plan_search_device(self, q_dev, k, out_idx, out_sim):
+        """A device-in / device-out search of fixed buffers as a zero-argument callable: the argument conversion
+        of ``search_batch_device`` (contiguity check, pointers, shapes) is done once, every call is one C-ABI call
+        on torch's current stream.  For loops that repeat a search of the same buffers faster than Python can
+        rebuild the arguments (a 32 us single-query kernel).  The tensors must stay alive and unchanged in
+        shape; their contents may change between calls."""
+        if not (self.world == 1 and self.local._h is not None and self.local.n >= k and q_dev.is_contiguous()
+                and out_idx.is_contiguous() and out_sim.is_contiguous()):
+            return lambda: self.search_batch_device(q_dev, k, out_idx, out_sim)
+        h = self.local._h
+        fn, hh = h.lib.cslam_nns_search, h.h
+        qp, oi, os_ = q_dev.data_ptr(), out_idx.data_ptr(), out_sim.data_ptr()
+        B, ld, dev_index = int(q_dev.shape[0]), int(q_dev.shape[1]), self.local._dev_index
+        raw_stream = torch._C._cuda_getCurrentRawStream if hasattr(torch._C, "_cuda_getCurrentRawStream") else \
+            (lambda i: torch.cuda.current_stream(i).cuda_stream)
+
+        def call():
+            rc = fn(hh, qp, B, ld, 1, k, oi, os_, 1, raw_stream(dev_index), None)
+            if rc:
+                _native.check(rc, hh)
+        return call
+
     def check_exchange(self):
         """Raise if a peer-memory exchange of an earlier ``search_batch_device`` call timed out (call after
         synchronising the stream)."""

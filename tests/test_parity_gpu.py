@@ -530,3 +530,14 @@ def test_search_batches_pipeline_equals_search_batch():
     got = list(sm.search_batches(iter(blocks), k))
     for (gi, gs), (wi, ws) in zip(got, want):
         assert np.array_equal(np.asarray(gi) + 1000, np.asarray(wi)) and np.array_equal(gs, ws)
+    # a prepared device call returns the bits of the ordinary one, also after the query buffer's contents change
+    qd = torch.from_numpy(blocks[0]).cuda()
+    oi = torch.empty((256, k), dtype=torch.int64, device="cuda")
+    os_ = torch.empty((256, k), dtype=torch.float32, device="cuda")
+    plan = sm.plan_search_device(qd, k, oi, os_)
+    for j in (0, 1, 3):
+        qd.copy_(torch.from_numpy(blocks[j]))
+        plan()
+        ri, rs = sm.search_batch_device(qd, k)
+        torch.cuda.synchronize()
+        assert torch.equal(ri, oi) and torch.equal(rs, os_)
