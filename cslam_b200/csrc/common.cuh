@@ -161,6 +161,69 @@ __device__ __forceinline__ u64 warp_merge_desc(u64 a, u64 b, int lane) {
   return v;
 }
 
+// ---- lists of up to 128 keys in registers: element i = r * 32 + lane of v[r], sorted descending, 0 = empty ----
+// (32 < k <= 128 of the single-query kernel; the k <= 32 code above with four registers per lane instead of one)
+
+// Offer one key per lane; `thr` mirrors element k - 1.  The list itself keeps up to 128 keys.
+__device__ __forceinline__ void offer_big(u64 (&v)[4], int k, u64 key, bool have, u64& thr, int lane) {
+  unsigned m = __ballot_sync(kFull, have && key > thr);
+  if (m == 0) return;  // the common case after warm-up
+  const int kr = (k - 1) >> 5, kl = (k - 1) & 31;
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    const u64 cand = __shfl_sync(kFull, key, src);
+    if (cand > thr) {
+      int pos = 0;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) pos += __popc(__ballot_sync(kFull, v[r] > cand));
+#pragma unroll
+      for (int r = 3; r >= 0; --r) {   // highest register first: v[r - 1] is still the old one when it is read
+        const u64 up = __shfl_up_sync(kFull, v[r], 1);
+        const u64 carry = r > 0 ? __shfl_sync(kFull, v[r > 0 ? r - 1 : 0], 31) : 0ull;
+        const int idx = r * 32 + lane;
+        if (idx > pos) v[r] = lane == 0 ? carry : up;
+        else if (idx == pos) v[r] = cand;
+      }
+      const u64 sel = kr == 0 ? v[0] : (kr == 1 ? v[1] : (kr == 2 ? v[2] : v[3]));
+      thr = __shfl_sync(kFull, sel, kl);
+    }
+  }
+}
+
+// a := the 128 largest keys of the union of two such lists, sorted.  C[i] = max(A[i], B[127 - i]) is bitonic and
+// holds exactly those keys; two register-level and five shuffle-level compare-exchange stages sort it.
+__device__ __forceinline__ void warp_merge_desc_big(u64 (&a)[4], const u64 (&b)[4], int lane) {
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const u64 br = __shfl_sync(kFull, b[3 - r], 31 - lane);
+    a[r] = a[r] > br ? a[r] : br;
+  }
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {   // distance 64: registers r and r + 2
+    const u64 hi = a[r] > a[r + 2] ? a[r] : a[r + 2], lo = a[r] > a[r + 2] ? a[r + 2] : a[r];
+    a[r] = hi;
+    a[r + 2] = lo;
+  }
+#pragma unroll
+  for (int r = 0; r < 4; r += 2) {   // distance 32: registers r and r + 1
+    const u64 hi = a[r] > a[r + 1] ? a[r] : a[r + 1], lo = a[r] > a[r + 1] ? a[r + 1] : a[r];
+    a[r] = hi;
+    a[r + 1] = lo;
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    u64 x = a[r];
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+      const u64 o = __shfl_xor_sync(kFull, x, j);
+      const bool want_max = (lane & j) == 0;
+      x = (want_max == (x > o)) ? x : o;
+    }
+    a[r] = x;
+  }
+}
+
 // Block-wide exact select: out[r] = the candidate with exactly r larger candidates, for r < k.
 // Keys are unique (they embed the row) except for empties (0), which are skipped.  `out[0..k)` must be
 // zeroed and visible to the block before the call; all threads of the block call it.  O(M^2 / threads)

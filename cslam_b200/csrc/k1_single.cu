@@ -181,8 +181,8 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
   long long nx_tile = p.n_chunks == 1 ? (long long)S : (long long)(S / p.n_chunks);
   int nx_chunk = p.n_chunks == 1 ? 0 : S % p.n_chunks;
   u64* my_list = lists + (size_t)warp * p.k;
-  if (p.k > 32) warp_list_clear(my_list, p.k, lane);
   u64 thr = 0ull, mine = 0ull;
+  u64 big[4] = {0ull, 0ull, 0ull, 0ull};   // 32 < k <= 128: the warp's list, four keys per lane (offer_big)
 
   const int lpr = 1 << p.lpr_log2;
   const int G = 32 >> p.lpr_log2;
@@ -247,7 +247,8 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
         if (p.all_sims) {
           if (valid) p.all_sims[row] = s_;
         } else {
-          offer(my_list, p.k, make_key(s_, (uint32_t)row), valid, thr, mine, lane);
+          if (p.k <= 32) offer(my_list, p.k, make_key(s_, (uint32_t)row), valid, thr, mine, lane);
+          else offer_big(big, p.k, make_key(s_, (uint32_t)row), valid, thr, lane);
         }
       }
       __syncwarp();
@@ -307,7 +308,8 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
         if (p.all_sims) {
           if (lane == 0) p.all_sims[row] = s_;
         } else {
-          offer(my_list, p.k, make_key(s_, (uint32_t)row), lane == 0, thr, mine, lane);
+          if (p.k <= 32) offer(my_list, p.k, make_key(s_, (uint32_t)row), lane == 0, thr, mine, lane);
+          else offer_big(big, p.k, make_key(s_, (uint32_t)row), lane == 0, thr, lane);
         }
         dot = 0.f;
         nn = 0.f;
@@ -434,82 +436,78 @@ __global__ void __launch_bounds__(W * 32, 1) k1_kernel(const K1Dev p) {
     return;
   }
 
-  // -- 32 < k <= 128: CTA merge -> scratch ------------------------------------------------------------
-  // [k], 8-byte aligned: `red` is, and flag sits W + 1 (odd) floats behind it, so flag + 3 is.  (Rounding the
-  // address up through uintptr_t would turn the accesses below into generic LD.E / ST.E.)
-  static_assert((W + 1) % 2 == 1, "cta_out alignment");
-  u64* cta_out = reinterpret_cast<u64*>(flag + 3);
-  if (p.k == 1) {
-    if (lane == 0) my_list[0] = thr;
-  } else if (p.k <= 32) {
-    if (lane < p.k) my_list[lane] = mine;
-  }
-  for (int i = tid; i < p.k; i += W * 32) cta_out[i] = 0ull;
-  __syncthreads();
-  block_rank_select(lists, W * p.k, p.k, cta_out);
-  __syncthreads();
-  for (int i = tid; i < p.k; i += W * 32) p.scratch[(size_t)blockIdx.x * p.k + i] = cta_out[i];
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    const unsigned t = atomicAdd(p.ticket, 1u);
-    *flag = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!*flag) return;
-
-  // -- last CTA: prune with tau = the best k-th key of any CTA (k candidates >= tau exist, so nothing
-  //    below it can be in the top-k), rank-select the survivors, decode, publish -------------------
-  __threadfence();
-  u64* surv = reinterpret_cast<u64*>(smem);  // the ring is idle now: every issued copy was consumed
-  int* cnt = flag + 1;
-  // tau: a lower bound of the global k-th key.  For a list position j, the m-th largest of the
-  // grid's j-th entries has at least m*(j+1) >= k keys at or above it when m = ceil(k/(j+1)).
-  // Try j+1 = 1, 2, 4, ... and j = k-1; keep the largest bound.
-  const int Gd = (int)gridDim.x;
-  u64* col = surv + (size_t)Gd * p.k;  // [grid] scratch column, behind the survivor buffer
-  u64* red64 = reinterpret_cast<u64*>(bars);  // barriers are dead as well: [0] = tau
-  if (tid == 0) {
-    red64[0] = 0ull;
-    *cnt = 0;
-  }
-  for (int i = tid; i < p.k; i += W * 32) cta_out[i] = 0ull;
-  __syncthreads();
-  for (int jp1 = 1;; jp1 *= 2) {
-    if (jp1 > p.k) jp1 = p.k;
-    const int m = (p.k + jp1 - 1) / jp1;
-    if (m <= Gd) {
-      for (int c = tid; c < Gd; c += W * 32) col[c] = __ldcg(p.scratch + (size_t)c * p.k + (jp1 - 1));
-      __syncthreads();
-      for (int c = tid; c < Gd; c += W * 32) {
-        const u64 v = col[c];
-        if (v == 0ull) continue;
-        int rank = 0;
-        for (int j = 0; j < Gd; ++j) rank += (col[j] > v) ? 1 : 0;
-        if (rank == m - 1) atomicMax(&red64[0], v);
+  // -- 32 < k <= 128: the k <= 32 scheme with four keys per lane (offer_big / warp_merge_desc_big).  The
+  //    shared-memory lists, rank selects and the tau pruning this replaced took 70 us at k = 33 against 44.5 us at
+  //    k = 32 (100k x 512). ------------------------------------------------------------------------------------
+  {
+    const int k = p.k;
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+      if (r * 32 + lane < k) my_list[r * 32 + lane] = big[r];
+    __syncthreads();
+    if (warp == 0) {
+      for (int w = 1; w < W; ++w) {
+        u64 o[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) o[r] = r * 32 + lane < k ? lists[(size_t)w * k + r * 32 + lane] : 0ull;
+        warp_merge_desc_big(big, o, lane);
       }
-      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (r * 32 + lane < k) p.scratch[(size_t)blockIdx.x * k + r * 32 + lane] = big[r];
+      __threadfence();
+      __syncwarp();
+      unsigned t = 0;
+      if (lane == 0) t = atomicAdd(p.ticket, 1u);
+      t = __shfl_sync(kFull, t, 0);
+      if (lane == 0) *flag = (t == gridDim.x - 1);
     }
-    if (jp1 == p.k) break;
+    __syncthreads();
+    if (!*flag) return;
+    __threadfence();
+    // the last CTA: warp w merges the CTA lists w, w + W, ... of the grid (two lists' loads in flight)
+#pragma unroll
+    for (int r = 0; r < 4; ++r) big[r] = 0ull;
+    const int G_ = (int)gridDim.x;
+    for (int c0 = warp; c0 < G_; c0 += 2 * W) {
+      u64 o0[4], o1[4];
+      const int c1 = c0 + W;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const bool in = r * 32 + lane < k;
+        o0[r] = in ? __ldcg(p.scratch + (size_t)c0 * k + r * 32 + lane) : 0ull;
+        o1[r] = (in && c1 < G_) ? __ldcg(p.scratch + (size_t)c1 * k + r * 32 + lane) : 0ull;
+      }
+      warp_merge_desc_big(big, o0, lane);
+      warp_merge_desc_big(big, o1, lane);
+    }
+    __syncthreads();  // everybody is past reading `lists` as the CTA merge's input
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+      if (r * 32 + lane < k) my_list[r * 32 + lane] = big[r];
+    __syncthreads();
+    if (warp == 0) {
+      for (int w = 1; w < W; ++w) {
+        u64 o[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) o[r] = r * 32 + lane < k ? lists[(size_t)w * k + r * 32 + lane] : 0ull;
+        warp_merge_desc_big(big, o, lane);
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int i = r * 32 + lane;
+        if (i < k) {
+          const u64 key = big[r];
+          const bool have = key != 0ull;
+          const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
+          if (p.out_keys) p.out_keys[i] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
+          if (p.out_idx) p.out_idx[i] = have ? grow : -1ll;
+          if (p.out_sim) p.out_sim[i] = have ? key_sim(key) : -INFINITY;
+        }
+      }
+      if (lane == 0) *p.ticket = 0u;
+    }
   }
-  const u64 tau = red64[0];
-  const int total = (int)gridDim.x * p.k;
-  for (int i = tid; i < total; i += W * 32) {
-    const u64 key = __ldcg(p.scratch + i);
-    if (key != 0ull && key >= tau) surv[atomicAdd(cnt, 1)] = key;
-  }
-  __syncthreads();
-  block_rank_select(surv, *cnt, p.k, cta_out);
-  __syncthreads();
-  for (int i = tid; i < p.k; i += W * 32) {
-    const u64 key = cta_out[i];
-    const bool have = key != 0ull;
-    const long long grow = (long long)key_row(key) * p.idx_stride + p.idx_offset;
-    if (p.out_keys) p.out_keys[i] = have ? ((key & 0xffffffff00000000ull) | (u64)(~(uint32_t)grow)) : 0ull;
-    if (p.out_idx) p.out_idx[i] = have ? grow : -1ll;
-    if (p.out_sim) p.out_sim[i] = have ? key_sim(key) : -INFINITY;
-  }
-  if (tid == 0) *p.ticket = 0u;
 }
 
 inline int ceil_log2(int v) {
@@ -602,9 +600,6 @@ cudaError_t k1_launch(const K1Args& a, const K1Tuning& t, int num_sms, cudaStrea
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
 
-  // the last CTA re-uses the ring as the survivor buffer of the final merge: grid * k keys
-  while (grid > 1 && (size_t)grid * (a.k + 1) * 8 > (size_t)W * p.stages * p.stage_bytes) --grid;
-  if ((size_t)grid * (a.k + 1) * 8 > (size_t)W * p.stages * p.stage_bytes) return cudaErrorInvalidConfiguration;
   const size_t smem = (size_t)W * p.stages * p.stage_bytes + fixed;
   p.tiles_div = tiles / (grid * W);
   p.tiles_rem = tiles % (grid * W);

@@ -179,6 +179,33 @@ def test_single_query_vs_oracle(M, n, d, k, dist):
     assert m._h.lib.cslam_nns_last_variant(m._h.h) == 1
 
 
+@pytest.mark.parametrize("n,d", [(30000, 96), (150000, 128), (6000, 2100), (40, 64)])
+def test_single_query_register_lists_33_to_128(M, n, d):
+    """32 < k <= 128: four keys per lane (offer_big / warp_merge_desc_big) on the register path, the chunked
+    path (rows longer than a stage), a grid of one CTA per SM, fewer rows than k, duplicated rows and a NaN row."""
+    db = synth.unit_rows(700 + n, n, d)
+    if n > 100:
+        db[17] = db[5]            # exact duplicates: the lower row must come first
+        db[n - 3] = db[5]
+        db[99] = 0.0              # becomes the NaN row below
+    qs = synth.queries_for(800 + n, db, 2)
+    qs[1] = db[5] * 3.0
+    m = build(M, db, bulk=True)
+    for k in (33, 40, 64, 65, 96, 127, 128):
+        for q in qs:
+            items, sims = m.search(q, k)
+            assert len(items) == min(k, n)
+            assert_parity(db, q, k, np.asarray(items), sims)
+    assert m._h.lib.cslam_nns_last_variant(m._h.h) == 1
+    if n > 100:   # a NaN similarity sorts first (torch.argsort descending), the rest is unchanged
+        want_items, want_sims = m.search(qs[0], 39)
+        db[99, 0] = np.nan
+        m2 = build(M, db, bulk=True)
+        items, sims = m2.search(qs[0], 40)
+        assert items[0] == 99 and np.isnan(sims[0])
+        assert list(items[1:]) == list(want_items) and np.array_equal(sims[1:], want_sims)
+
+
 def test_unnormalised_rows_and_queries(M):
     db = (synth.uniform(5, (600, 40)) * 7.0 - 2.0).astype(np.float32)
     q = (synth.uniform(6, (40,)) * 3.0).astype(np.float32)
