@@ -114,6 +114,19 @@ __device__ __forceinline__ void st_cluster_f32(float* p, uint32_t cta, float v) 
 __device__ __forceinline__ void fence_acq_rel_cluster() {
   asm volatile("fence.acq_rel.cluster;" ::: "memory");
 }
+// Copy `bytes` (multiple of 16) of this CTA's shared memory to the SAME offset in CTA `peer` of the cluster with the
+// bulk-copy engine; the bytes are counted (complete_tx) on the mbarrier at `bar`'s offset in the peer.  Waiters on
+// that barrier see the data without any cluster-scope fence, like the bytes of a TMA load.
+__device__ __forceinline__ void bulk_s2peer(const void* src, uint32_t bytes, uint64_t* bar, uint32_t peer) {
+  asm volatile(
+      "{\n\t.reg .b32 rd, rb;\n\t"
+      "mapa.shared::cluster.u32 rd, %0, %3;\n\t"
+      "mapa.shared::cluster.u32 rb, %2, %3;\n\t"
+      "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [rd], [%0], %1, [rb];\n\t}" ::"r"(
+          smem_u32(src)),
+      "r"(bytes), "r"(smem_u32(bar)), "r"(peer)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -283,7 +296,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
       mbar_init(&acc_empty[a], 16);
-      mbar_init(&norm_bar[a], 8);
+      mbar_init(&norm_bar[a], 4);   // the 4 local converter warps; the peer's half arrives as 4 x 256 tx bytes
     }
     mbar_fence_init();
   }
@@ -433,15 +446,20 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       QPROF_WAIT(wce, mbar_wait(&acc_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
       float* ninv = norms + a * (2 * BN2) + rank * BM + r;
       const float inv = rsqrtf(fmaxf(nn, kEps * kEps));  // 1 / max(|x|, eps)
+      // Both epilogues need all 256 rows: this warp's 32 rows go into the local arrays with plain stores and into
+      // the peer's with two 128-byte bulk copies that complete on the PEER's norm barrier, while the local barrier
+      // is told to expect the peer's 256 bytes for the same rows of its half.  (st.shared::cluster + fence.acq_rel
+      // .cluster on both sides cost the converter ~2.2k clk and every epilogue warp ~0.9k clk per tile, a quarter
+      // of a 256-float tile's time.)  The source is not rewritten before both epilogues have released tile t
+      // (acc_empty above), by which time the peer has long consumed the copy.
       ninv[0] = inv;
       ninv[BN2] = sx;
-      st_cluster_f32(ninv, rank ^ 1u, inv);
-      st_cluster_f32(ninv + BN2, rank ^ 1u, sx);
-      QPROF_WAIT(wcf, fence_acq_rel_cluster());
+      QPROF_WAIT(wcf, fence_proxy_async());   // generic-proxy stores -> visible to the bulk-copy engine
       __syncwarp();
       if (lane == 0) {
-        mbar_arrive(&norm_bar[a]);
-        mbar_arrive_cluster(&norm_bar[a], rank ^ 1u);
+        mbar_expect_tx(&norm_bar[a], 256u);   // = arrive + expect: our 32 rows are in, the peer's 2 x 128 B are due
+        bulk_s2peer(ninv, 128u, &norm_bar[a], rank ^ 1u);
+        bulk_s2peer(ninv + BN2, 128u, &norm_bar[a], rank ^ 1u);
       }
     }
     if (p.prof && tid == 8 * 32) {
@@ -494,7 +512,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
         }
       }
       QPROF_WAIT(wnorm, mbar_wait(&norm_bar[a], ph));
-      QPROF_WAIT(wfence, fence_acq_rel_cluster());  // the peer's half of norms[a] came through st.shared::cluster
+      // (no cluster fence: the peer's half of norms[a] came as bulk-copy bytes counted on norm_bar)
       QPROF_WAIT(wepi, mbar_wait(&acc_full[a], ph));
       tc_fence_after();
       const long long tscan0 = p.prof ? clock64() : 0;
