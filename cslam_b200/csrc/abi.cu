@@ -405,10 +405,12 @@ int search_device(cslam_nns_t h, const float* dq, long long B, long long q_ld, i
       // kernel on 8 GPUs.  With the bound of a 1/S sample only the ~S * kl best rows of a query ever enter a list.
       // The sample is small (seed_rows rows in all) so that its own warm-up stays cheap.  Short rows only: with
       // long rows (dim > 1024) a tile's products take far longer than its epilogue and the warm-up is hidden.
-      // Sample size: one 256-row tile per CTA pair (18 944 rows) up to 2.5M rows, up to four for larger databases
-      // (10M x 256: 2.95 ms per batch with one tile, 2.84 with four, no better with eight; 1.25M x 256: one is best).
-      long long tiles_per_pair = h->n / 2500000;
-      tiles_per_pair = tiles_per_pair < 1 ? 1 : (tiles_per_pair > 4 ? 4 : tiles_per_pair);
+      // Sample size: 1-8 256-row tiles per CTA pair (18 944 rows each), one per 312 500 rows of 256 floats — a
+      // tile of the sample costs ~2.6 us at 256 floats (its epilogue is a running maximum) and a 4x larger sample
+      // leaves a quarter of the rows above the seed for the full pass's insertion rounds (1.25M x 256: kernel
+      // 0.304 -> 0.265 ms with four tiles); longer rows get proportionally fewer tiles.
+      long long tiles_per_pair = h->n / (312500ll * ((h->dim + 255) / 256));
+      tiles_per_pair = tiles_per_pair < 1 ? 1 : (tiles_per_pair > 8 ? 8 : tiles_per_pair);
       const long long sample_rows = h->seed_rows > 0 ? h->seed_rows : 18944 * tiles_per_pair;
       long long stride = h->seed_stride > 0 ? h->seed_stride : h->n / sample_rows;
       if (stride > 1 && h->n >= h->seed_min_rows && h->dim <= h->seed_max_dim) {

@@ -181,6 +181,31 @@ __device__ __forceinline__ uint32_t select32(const uint32_t (&v)[32], int j) {
   const uint32_t d0 = (j & 8) ? c[1] : c[0], d1 = (j & 8) ? c[3] : c[2];
   return (j & 16) ? d1 : d0;
 }
+// max that returns NaN when either operand is NaN (fmaxf drops NaNs; a NaN similarity must reach the exact test)
+__device__ __forceinline__ float max_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t select16(const uint32_t (&v)[16], int j) {
+  uint32_t a[8], b[4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) b[i] = (j & 2) ? a[2 * i + 1] : a[2 * i];
+  const uint32_t c0 = (j & 4) ? b[1] : b[0], c1 = (j & 4) ? b[3] : b[2];
+  return (j & 8) ? c1 : c0;
+}
+// tcgen05.wait::ld that names the 16 registers of the load it completes, so that no use of them can be scheduled
+// above it (another load may be in flight into a second set of registers at the same time)
+__device__ __forceinline__ void tmem_ld_wait16(uint32_t (&v)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]),
+                 "+r"(v[15])
+               :
+               : "memory");
+}
 // Smallest entry of lst[lo .. hi) and its position (entries are [j * BM] apart).
 __device__ __forceinline__ void group_min(const u64* lst, int lo, int hi, u64& mk, int& mp) {
   mk = ~0ull;
@@ -498,6 +523,11 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     // query — full or not — drops candidates below the best bound published so far (read once per tile).
     // This removes most of the k ln(rows/k) insertions per list, which diverge lane by lane.
     unsigned* gq = (valid && p.gthr != nullptr && !(p.dbg & 64)) ? p.gthr + q : nullptr;
+    // Seeding sample pass (k == 1, no shared bound): the thread's best row is a running maximum in registers, no
+    // list and no insertion rounds at all
+    const bool max_only = p.k == 1 && p.gthr == nullptr;   // uniform over the grid (gq is per lane: a warp-wide vote follows)
+    float best_u = -INFINITY;
+    uint32_t best_row = 0xffffffffu;
     long long wepi = 0, wnorm = 0, wfence = 0, wscan = 0;
     for (long long t = 0; t < my_tiles; ++t) {
       const int a = (int)(t & 1);
@@ -518,35 +548,58 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       const long long tscan0 = p.prof ? clock64() : 0;
       const float* ninv = norms + a * (2 * BN2);
       const float* nsum = ninv + BN2;
-      for (int c0 = eh * (BN2 / 2); c0 < (eh + 1) * (BN2 / 2); c0 += 32) {
-        if (c0 >= valid_cols || (p.dbg & 4)) break;
-        uint32_t v[32];
-        if (!(p.dbg & 32)) {
-          tmem_ld_32x32b_x32(tmem_base + lane_base + (uint32_t)(a * BN2 + c0), v);
-          tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0u;
+      // 8 chunks of 16 columns, two register sets: the tcgen05.ld of chunk i + 1 is in flight while chunk i is
+      // scanned (one 32-column load followed by its scan left the ~250 clk of the load exposed four times per tile,
+      // and with two epilogue warps per scheduler there is little else to hide it).
+      auto scan16 = [&](uint32_t (&v)[16], int c0) {
+        if (c0 >= valid_cols || (p.dbg & 4)) return;
+        if (p.dbg & 32) {   // development: TMEM loads only (keeps the registers live), no scan
+          if (v[0] == 0x7fc12345u && v[15] == 0x7fc54321u) ts.g_seen ^= 1u;
+          return;
         }
-        // fast path: no branches, one survivor bit per column (the threshold is only read here; a stale
-        // value just sends a few extra candidates to the exact comparison below)
-        uint32_t m = 0u;
+        // fast path: u = (c sum(x) + acc) / |x| for the 16 columns with packed fp32x2 instructions (same roundings as
+        // fmaf / a multiply) and their NaN-propagating maximum: 2.5 issue slots per column.  Only when some lane's
+        // maximum reaches its bound (the bound is only read here; a stale value just sends the warp to the exact
+        // test below for nothing) is the per-column survivor mask built.  The per-column FSETP / SEL / IADD3 this
+        // replaced made the epilogue issue-bound at 256-float rows: 2.9k clk per tile against 1k for the bare loads.
+        float mx = -INFINITY;
+        const float2 qm2 = make_float2(qmean_r, qmean_r);
 #pragma unroll
-        for (int j4 = 0; j4 < 32; j4 += 4) {
+        for (int j4 = 0; j4 < 16; j4 += 4) {
           const float4 iv = *reinterpret_cast<const float4*>(ninv + c0 + j4);
           const float4 sm = *reinterpret_cast<const float4*>(nsum + c0 + j4);
-          const float iv_[4] = {iv.x, iv.y, iv.z, iv.w};
-          const float sm_[4] = {sm.x, sm.y, sm.z, sm.w};
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            const float u_ = fmaf(qmean_r, sm_[jj], __uint_as_float(v[j4 + jj])) * iv_[jj];
-            v[j4 + jj] = __float_as_uint(u_);
-            // ties go to the exact key comparison (a lower row index wins); NaN passes and sorts first
-            m |= (!(u_ < ts.thr_u) && c0 + j4 + jj < valid_cols) ? (1u << (j4 + jj)) : 0u;
-          }
+          const float2 u01 = __fmul2_rn(__ffma2_rn(qm2, make_float2(sm.x, sm.y),
+                                                   make_float2(__uint_as_float(v[j4]), __uint_as_float(v[j4 + 1]))),
+                                        make_float2(iv.x, iv.y));
+          const float2 u23 = __fmul2_rn(__ffma2_rn(qm2, make_float2(sm.z, sm.w),
+                                                   make_float2(__uint_as_float(v[j4 + 2]), __uint_as_float(v[j4 + 3]))),
+                                        make_float2(iv.z, iv.w));
+          v[j4] = __float_as_uint(u01.x);
+          v[j4 + 1] = __float_as_uint(u01.y);
+          v[j4 + 2] = __float_as_uint(u23.x);
+          v[j4 + 3] = __float_as_uint(u23.y);
+          mx = max_nan(max_nan(mx, u01.x), max_nan(u01.y, max_nan(u23.x, u23.y)));
         }
+        if (max_only) {
+          if (valid && mx > best_u) {   // NaN and the zero rows past the end of the last tile never win
+            int jb = 0;
+#pragma unroll
+            for (int jj = 15; jj >= 0; --jj) jb = (__uint_as_float(v[jj]) == mx) ? jj : jb;   // first column of the maximum
+            if (c0 + jb < valid_cols) {
+              best_u = mx;
+              best_row = (uint32_t)(row_base + c0 + jb);
+            }
+          }
+          return;
+        }
+        if (!__any_sync(kFull, valid && !(mx < ts.thr_u))) return;
+        // ties go to the exact key comparison (a lower row index wins); NaN passes and sorts first
+        uint32_t m = 0u;
+#pragma unroll
+        for (int jj = 0; jj < 16; ++jj) m |= !(__uint_as_float(v[jj]) < ts.thr_u) ? (1u << jj) : 0u;
+        if (c0 + 16 > valid_cols) m &= (1u << (valid_cols - c0)) - 1u;   // the database's last, partial tile
         if (!valid || (p.dbg & 16)) m = 0u;
-        // slow path, CONVERGENT: every lane pops its own next survivor (its value is picked out of the 32
+        // slow path, CONVERGENT: every lane pops its own next survivor (its value is picked out of the 16
         // registers by a select tree) and all lanes run the insertion together, each on its own list; a lane
         // without a survivor rides along with key 0.  Rounds per chunk = the largest survivor count of any
         // lane (1-2 after warm-up), where a branch per column served one lane at a time.
@@ -554,7 +607,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           const int j = m != 0u ? __ffs(m) - 1 : 0;
           const bool has = m != 0u;
           m &= m - 1u;
-          const float s_ = __uint_as_float(select32(v, j)) * invq_r;
+          const float s_ = __uint_as_float(select16(v, j)) * invq_r;
           const u64 key = (has && !(s_ < ts.thr))
                               ? (((u64)sim_to_ord(s_) << 32) | (u64)(~(uint32_t)(row_base + c0 + j)))
                               : 0ull;
@@ -567,9 +620,24 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
           if (__any_sync(kFull, ts.thr_u != thr_was)) {
             uint32_t keep = 0u;
 #pragma unroll
-            for (int jj = 0; jj < 32; ++jj) keep |= !(__uint_as_float(v[jj]) < ts.thr_u) ? (1u << jj) : 0u;
+            for (int jj = 0; jj < 16; ++jj) keep |= !(__uint_as_float(v[jj]) < ts.thr_u) ? (1u << jj) : 0u;
             m &= keep;
           }
+        }
+      };
+      {
+        uint32_t va[16], vb[16];
+        const uint32_t t0 = tmem_base + lane_base + (uint32_t)(a * BN2 + eh * (BN2 / 2));
+        const int cb = eh * (BN2 / 2);
+        tmem_ld_32x32b_x16(t0, va);
+#pragma unroll 1
+        for (int i = 0; i < (BN2 / 2) / 16; i += 2) {
+          tmem_ld_wait16(va);
+          tmem_ld_32x32b_x16(t0 + (uint32_t)((i + 1) * 16), vb);
+          scan16(va, cb + i * 16);
+          tmem_ld_wait16(vb);
+          if (i + 2 < (BN2 / 2) / 16) tmem_ld_32x32b_x16(t0 + (uint32_t)((i + 2) * 16), va);
+          scan16(vb, cb + (i + 1) * 16);
         }
       }
       if (ts.dirty) {  // this list's bound grew during the tile: one atomic per list and tile at most
@@ -591,6 +659,7 @@ k2q_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
       p.prof[blockIdx.x * 16 + 10] = (u64)wscan;
     }
     // this thread's list -> part_keys[2 * pair + column half][q][k]
+    if (max_only && valid) lst[0] = best_row != 0xffffffffu ? make_key(best_u * invq_r, best_row) : 0ull;
     if (valid) {
       u64* out = p.part_keys + ((size_t)(2 * pair + eh) * p.B + q) * p.k;
       for (int j = 0; j < p.k; ++j) out[j] = lst[j * BM];
