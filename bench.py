@@ -429,6 +429,9 @@ def run_swarm(args, steps, warmup, cpu_budget=12.0):
         if r == 1:
             probe = x[:4096].cpu().numpy()
         del x
+    # host-timed leg: let the worker threads of the previous leg's CPU baseline (OpenMP pools spin for a while after
+    # a parallel region) go idle before anything is timed on the host
+    time.sleep(1.0)
     nq = warmup + steps
     rng = np.random.default_rng(5)
     qs = rng.random((nq, dim)).astype(np.float32)
