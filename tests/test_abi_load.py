@@ -128,3 +128,20 @@ def test_integer_item_tracking_for_the_device_filter():
         m2._note_ids([7, bad])
         assert not m2._ids_ok and m2._ids_pending == []
     assert not M().ids_on_device        # nothing allocated yet
+
+
+def test_items_lookup_helpers_need_no_gpu():
+    """Row -> item mapping of the batched calls (one C-level itemgetter call per block; identity for bulk shards)."""
+    import numpy as np
+    from cslam_b200 import NearestNeighborsMatching
+    from cslam_b200.sharded import RowIdentity, ShardedNearestNeighborsMatching
+    m = object.__new__(NearestNeighborsMatching)   # the constructor needs a CUDA device (it fails loudly without)
+    m.items = {0: "a", 1: "b", 2: ("c", 3), 3: None}
+    assert m._items_of(np.array([[0, 1], [3, 2]])) == [["a", "b"], [None, ("c", 3)]]
+    assert m._items_of(np.array([[2]])) == [[("c", 3)]]
+    assert m._items_of(np.empty((3, 0), np.int64)) == [[], [], []]
+    s = object.__new__(ShardedNearestNeighborsMatching)
+    s.items = RowIdentity()
+    assert s._items_of(np.array([[5, 7], [9, 11]])) == [[5, 7], [9, 11]]
+    s.items = {5: "x", 7: "y"}
+    assert s._items_of(np.array([[7, 5]])) == [["y", "x"]]
