@@ -102,18 +102,6 @@ __device__ __forceinline__ float q_tf32_rna(float x) {
   return __uint_as_float(r);
 }
 
-// store to the same shared-memory offset in CTA `cta` of the cluster
-__device__ __forceinline__ void st_cluster_f32(float* p, uint32_t cta, float v) {
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "st.shared::cluster.f32 [ra], %2;\n\t}" ::"r"(smem_u32(p)),
-      "r"(cta), "f"(v)
-      : "memory");
-}
-__device__ __forceinline__ void fence_acq_rel_cluster() {
-  asm volatile("fence.acq_rel.cluster;" ::: "memory");
-}
 // Copy `bytes` (multiple of 16) of this CTA's shared memory to the SAME offset in CTA `peer` of the cluster with the
 // bulk-copy engine; the bytes are counted (complete_tx) on the mbarrier at `bar`'s offset in the peer.  Waiters on
 // that barrier see the data without any cluster-scope fence, like the bytes of a TMA load.
@@ -127,20 +115,6 @@ __device__ __forceinline__ void bulk_s2peer(const void* src, uint32_t bytes, uin
       "r"(bytes), "r"(smem_u32(bar)), "r"(peer)
       : "memory");
 }
-__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
-        "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]),
-        "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]),
-        "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr)
-      : "memory");
-}
-
 #define QPROF_WAIT(acc, stmt)                   \
   do {                                          \
     if (p.prof) {                               \
@@ -169,24 +143,13 @@ __device__ __forceinline__ void top_set_threshold(TopState& st, float thr, float
   const float t_ = thr / invq;
   st.thr_u = t_ - fabsf(t_) * 4.8e-7f;
 }
-// v[j] for a lane-dependent j without local memory: a 5-level select tree (31 selects)
-__device__ __forceinline__ uint32_t select32(const uint32_t (&v)[32], int j) {
-  uint32_t a[16], b[8], c[4];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) a[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) b[i] = (j & 2) ? a[2 * i + 1] : a[2 * i];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) c[i] = (j & 4) ? b[2 * i + 1] : b[2 * i];
-  const uint32_t d0 = (j & 8) ? c[1] : c[0], d1 = (j & 8) ? c[3] : c[2];
-  return (j & 16) ? d1 : d0;
-}
 // max that returns NaN when either operand is NaN (fmaxf drops NaNs; a NaN similarity must reach the exact test)
 __device__ __forceinline__ float max_nan(float a, float b) {
   float r;
   asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
   return r;
 }
+// v[j] for a lane-dependent j without local memory: a 4-level select tree (15 selects)
 __device__ __forceinline__ uint32_t select16(const uint32_t (&v)[16], int j) {
   uint32_t a[8], b[4];
 #pragma unroll
