@@ -46,6 +46,8 @@ SEARCH_CASES = [
     ("d4096_n96_k10", "rand", 96, 4096, 10, 4, 17),        # NetVLAD-shaped rows (16 KB)
     ("d3_n9_k20", "rand", 9, 3, 20, 4, 18),                # k > n
     ("d130_n300_k300", "rand", 300, 130, 300, 3, 19),      # k > 128: full ranking
+    ("d96_n3000_k40", "rand", 3000, 96, 40, 4, 31),        # 32 < k <= 128: the register lists of four keys per lane
+    ("d64_n2500_k128_randn", "randn", 2500, 64, 128, 4, 32),
 ]
 
 
